@@ -1,0 +1,282 @@
+"""Batched fitness evaluation on a B200: the drop-in for the reference's evaluation call sites.
+
+Reference boundary:
+  * evaluate_policy_standalone((idx, code)) -> (idx, code, score)   funsearch/funsearch_integration.py:30-64
+  * SimpleFunSearch._evaluate_policy_full(code) -> Optional[float]    funsearch/funsearch_integration.py:433-459
+  * the ProcessPoolExecutor block that maps the former over a generation          :535-540
+  * EvaluationResults / get_policy_score                               simulator/evaluator.py:16-25, 101-127
+
+`BatchEvaluator` holds traces and one cluster resident in HBM and evaluates any number of
+(policy, trace) episodes with ONE launch of the replay kernel.  PyTorch is used for device
+buffers, streams and (multi-GPU) torch.distributed only; every episode runs in the CUDA kernel
+of libks_b200.so.  No CPU path exists: without the library or without a GPU the calls raise.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from dataclasses import dataclass
+from typing import Iterable, List, Optional, Sequence, Tuple
+
+import numpy as np
+
+from . import _native as nat
+from .policy_compiler import CompiledPolicy, PolicyCompileError, compile_policy
+from .workload import ClusterSpec, Trace
+
+
+@dataclass
+class EvaluationResults:
+    """Same fields as the reference's EvaluationResults (simulator/evaluator.py:16-25)."""
+    avg_cpu_utilization: float
+    avg_memory_utilization: float
+    avg_gpu_count_utilization: float
+    avg_gpu_memory_utilization: float
+    gpu_fragmentation_score: float
+    num_snapshots: int
+    num_fragmentation_events: int
+
+
+@dataclass
+class EpisodeOutcome:
+    """One replayed episode."""
+    status: int
+    policy_score: float                      # get_policy_score(); 0 for a failed episode (:63-64)
+    results: Optional[EvaluationResults]     # None when no snapshot was taken (evaluator.py:79-80)
+    events: int
+    attempts: int
+    scorer_calls: int
+    placed: int
+    max_nodes: int
+    max_waiting: int
+    last_event_time: int
+    device_cycles: int
+    # only with want_placements: per pod, in pod_list order
+    final_creation_time: Optional[np.ndarray] = None
+    node_index: Optional[np.ndarray] = None   # -1 = never placed
+    gpu_mask: Optional[np.ndarray] = None
+
+    @property
+    def status_name(self) -> str:
+        return nat.STATUS_NAMES.get(self.status, str(self.status))
+
+    def placement_order(self, id_rank: np.ndarray) -> np.ndarray:
+        """Pods in order of successful placement.  Events pop in non-decreasing (time, id_rank)
+        order and a placement happens at its pod's final creation time, so sorting placed pods by
+        (final time, id_rank) reproduces the order."""
+        placed = np.nonzero(self.node_index >= 0)[0]
+        key = np.lexsort((id_rank[placed], self.final_creation_time[placed]))
+        return placed[key]
+
+
+class BatchEvaluator:
+    """Traces + one cluster resident on one GPU; evaluates batches of episodes."""
+
+    def __init__(self, cluster: ClusterSpec, traces: Sequence[Trace], device: int = 0,
+                 snapshot_interval: float = 0.05, cache_dir: Optional[str] = None):
+        import torch  # device buffers only
+        self._torch = torch
+        if not torch.cuda.is_available():
+            raise nat.KsError(-2, "no CUDA device: the batched evaluator has no CPU fallback")
+        self.device = torch.device("cuda", device)
+        self.lib = nat.lib()
+        nat.check(self.lib.ks_init(device))
+        if cache_dir:
+            nat.check(self.lib.ks_set_cache_dir(cache_dir.encode()))
+        self.cluster = cluster
+        self.traces = list(traces)
+        self.snapshot_interval = snapshot_interval
+        nconst, totals = cluster.packed()
+        self._totals = totals
+        self._nconst = torch.from_numpy(nconst).to(self.device)
+        self._trace_bufs = []
+        table = np.zeros((len(self.traces), 4), dtype=np.int64)
+        for i, tr in enumerate(self.traces):
+            _rank, podrec, heap0, place0 = tr.packed()
+            d_pod = torch.from_numpy(podrec).to(self.device)
+            d_heap = torch.from_numpy(heap0.view(np.int64)).to(self.device)
+            d_place = torch.from_numpy(place0.view(np.int64)).to(self.device)
+            self._trace_bufs.append((d_pod, d_heap, d_place))
+            table[i] = (d_pod.data_ptr(), d_heap.data_ptr(), d_place.data_ptr(), tr.n_pods)
+        self._trace_table = torch.from_numpy(table).to(self.device)
+        self.max_pods = max([t.n_pods for t in self.traces] + [1])
+        self._programs = {}
+        self._scratch = None
+        self.last_plan = None
+        self.last_kernel_ms = None
+
+    # ------------------------------------------------------------------ policies
+    def compile(self, sources: Sequence[str], threads: int = 0) -> List[Optional[CompiledPolicy]]:
+        """Python policy sources -> device functions (translate, then NVRTC in parallel).
+        A source outside the supported subset yields None (its episodes report status 'unsupported')."""
+        out: List[Optional[CompiledPolicy]] = []
+        todo = []
+        for src in sources:
+            try:
+                cp = compile_policy(src)
+                out.append(cp)
+                todo.append(cp)
+            except PolicyCompileError:
+                out.append(None)
+        uniq = {cp.symbol: cp for cp in todo if cp.handle is None}
+        if uniq:
+            cps = list(uniq.values())
+            n = len(cps)
+            srcs = (C.c_char_p * n)(*[cp.cuda_source.encode() for cp in cps])
+            syms = (C.c_char_p * n)(*[cp.symbol.encode() for cp in cps])
+            handles = (C.c_longlong * n)()
+            status = (C.c_int * n)()
+            nat.check(self.lib.ks_policy_compile_many(n, srcs, syms, threads, handles, status))
+            for i, cp in enumerate(cps):
+                if status[i] != 0:
+                    raise nat.KsError(status[i], "NVRTC rejected translated policy:\n" +
+                                      self.lib.ks_compile_log().decode(errors="replace") + "\n" + cp.cuda_source)
+                cp.handle = int(handles[i])
+            for cp in todo:
+                if cp.handle is None:
+                    cp.handle = uniq[cp.symbol].handle
+        return out
+
+    def _program(self, handles: Tuple[int, ...]) -> int:
+        prog = self._programs.get(handles)
+        if prog is None:
+            arr = (C.c_longlong * len(handles))(*handles)
+            out = C.c_longlong(-1)
+            nat.check(self.lib.ks_program_link(len(handles), arr, C.byref(out)))
+            prog = out.value
+            self._programs[handles] = prog
+        return prog
+
+    # ------------------------------------------------------------------ evaluation
+    def plan(self, n_episodes: int, want_placements: bool, max_pods: Optional[int] = None,
+             teams_per_block: int = 0, heap_smem_entries: int = 0) -> nat.KsPlan:
+        p = nat.KsPlan()
+        p.n_episodes = n_episodes
+        p.n_nodes = self.cluster.n_nodes
+        p.max_pods = max_pods or self.max_pods
+        p.want_placements = 1 if want_placements else 0
+        p.teams_per_block = teams_per_block
+        p.heap_smem_entries = heap_smem_entries
+        nat.check(self.lib.ks_plan(C.byref(p)))
+        return p
+
+    def run_episodes(self, policies: Sequence[CompiledPolicy], ep_policy: Sequence[int], ep_trace: Sequence[int],
+                     want_placements: bool = False, max_events: int = 0, teams_per_block: int = 0,
+                     heap_smem_entries: int = 0, stream=None) -> List[EpisodeOutcome]:
+        """Evaluate episodes e = (policies[ep_policy[e]], traces[ep_trace[e]]) in one kernel launch."""
+        torch = self._torch
+        n_ep = len(ep_policy)
+        if n_ep == 0:
+            return []
+        handles = tuple(int(p.handle) for p in policies)
+        prog = self._program(handles)
+        ep_policy = np.ascontiguousarray(ep_policy, dtype=np.int32)
+        ep_trace = np.ascontiguousarray(ep_trace, dtype=np.int32)
+        if ep_policy.min() < 0 or ep_policy.max() >= len(handles) or ep_trace.min() < 0 or ep_trace.max() >= len(self.traces):
+            raise ValueError("episode table refers to an unknown policy or trace")
+        pods_per_ep = np.array([self.traces[t].n_pods for t in ep_trace], dtype=np.int64)
+        plan = self.plan(n_ep, want_placements, int(pods_per_ep.max()), teams_per_block, heap_smem_entries)
+        self.last_plan = plan
+        with torch.cuda.device(self.device):
+            d_pol = torch.from_numpy(ep_policy).to(self.device)
+            d_tr = torch.from_numpy(ep_trace).to(self.device)
+            d_res = torch.empty(n_ep * nat.RESULT_DTYPE.itemsize, dtype=torch.uint8, device=self.device)
+            if self._scratch is None or self._scratch.numel() < plan.scratch_bytes:
+                self._scratch = torch.empty(int(plan.scratch_bytes), dtype=torch.uint8, device=self.device)
+            d_place = d_off = None
+            if want_placements:
+                padded = (pods_per_ep + 1) // 2 * 2
+                off = np.concatenate([[0], np.cumsum(padded)[:-1]]).astype(np.int64)
+                d_off = torch.from_numpy(off).to(self.device)
+                d_place = torch.empty(int(padded.sum()), dtype=torch.int64, device=self.device)
+            b = nat.KsBatch()
+            b.traces = self._trace_table.data_ptr()
+            b.ep_policy = d_pol.data_ptr()
+            b.ep_trace = d_tr.data_ptr()
+            b.nconst = self._nconst.data_ptr()
+            b.results = d_res.data_ptr()
+            b.placements = d_place.data_ptr() if want_placements else None
+            b.place_off = d_off.data_ptr() if want_placements else None
+            b.scratch = self._scratch.data_ptr()
+            for k in range(4):
+                b.totals[k] = int(self._totals[k])
+            b.max_events = max_events
+            b.snapshot_interval = self.snapshot_interval
+            st = stream or torch.cuda.current_stream(self.device)
+            e0 = torch.cuda.Event(enable_timing=True)
+            e1 = torch.cuda.Event(enable_timing=True)
+            e0.record(st)
+            nat.check(self.lib.ks_eval_batch(prog, C.byref(plan), C.byref(b), C.c_void_p(st.cuda_stream)))
+            e1.record(st)
+            res = np.frombuffer(d_res.cpu().numpy().tobytes(), dtype=nat.RESULT_DTYPE)
+            self.last_kernel_ms = e0.elapsed_time(e1)
+            place = d_place.cpu().numpy().view(np.uint64) if want_placements else None
+        out = []
+        for e in range(n_ep):
+            r = res[e]
+            results = None
+            if r["num_snapshots"] > 0:
+                results = EvaluationResults(float(r["avg_cpu_utilization"]), float(r["avg_memory_utilization"]),
+                                            float(r["avg_gpu_count_utilization"]), float(r["avg_gpu_memory_utilization"]),
+                                            float(r["gpu_fragmentation_score"]), int(r["num_snapshots"]),
+                                            int(r["num_fragmentation_events"]))
+            oc = EpisodeOutcome(int(r["status"]), float(r["policy_score"]), results, int(r["events"]), int(r["attempts"]),
+                                int(r["scorer_calls"]), int(r["placed"]), int(r["max_nodes"]), int(r["max_waiting"]),
+                                int(r["last_event_time"]), int(r["device_cycles"]))
+            if want_placements:
+                tr = self.traces[ep_trace[e]]
+                rank = tr.packed()[0]
+                rec = place[off[e]: off[e] + tr.n_pods][rank]   # rank-indexed -> pod_list order
+                node = ((rec >> np.uint64(8)) & np.uint64(0xFFFF)).astype(np.int64)
+                oc.final_creation_time = (rec >> np.uint64(24)).astype(np.int64)
+                oc.node_index = np.where(node >= nat.KS_NODE_WAITING, -1, node)
+                oc.gpu_mask = (rec & np.uint64(0xFF)).astype(np.int64)
+            out.append(oc)
+        return out
+
+    # ------------------------------------------------------------------ reference-shaped entry points
+    def evaluate_population(self, codes: Sequence[str], trace_ids: Optional[Sequence[int]] = None) -> List[float]:
+        """Fitness of every policy source of a generation: the batched replacement of the
+        ProcessPoolExecutor block (funsearch_integration.py:535-562).  With several traces the fitness
+        is the mean policy score over `trace_ids` (default: all resident traces).  A policy that fails to
+        translate, raises, or leaves the supported subset scores 0, like the reference's worker (:63-64)."""
+        trace_ids = list(range(len(self.traces))) if trace_ids is None else list(trace_ids)
+        compiled = self.compile(codes)
+        ok = [cp for cp in compiled if cp is not None]
+        uniq, slot = [], {}
+        for cp in ok:
+            if cp.symbol not in slot:
+                slot[cp.symbol] = len(uniq)
+                uniq.append(cp)
+        ep_pol, ep_tr, owner = [], [], []
+        for i, cp in enumerate(compiled):
+            if cp is None:
+                continue
+            for t in trace_ids:
+                ep_pol.append(slot[cp.symbol])
+                ep_tr.append(t)
+                owner.append(i)
+        scores = [0.0] * len(codes)
+        if ep_pol:
+            outs = self.run_episodes(uniq, ep_pol, ep_tr)
+            acc = [0.0] * len(codes)
+            for o, i in zip(outs, owner):
+                acc[i] += o.policy_score if o.status == nat.ST_OK else 0.0
+            scores = [a / len(trace_ids) for a in acc]
+        return scores
+
+    def evaluate_policy_standalone(self, policy_data: Tuple[int, str]) -> Tuple[int, str, float]:
+        """Same signature and error behaviour as funsearch_integration.py:30-64."""
+        idx, code = policy_data
+        try:
+            return (idx, code, self.evaluate_population([code], [0])[0])
+        except Exception:  # noqa: BLE001 -- the reference swallows everything into score 0
+            return (idx, code, 0)
+
+
+def evaluate_population(codes: Sequence[str], cluster: Optional[ClusterSpec] = None,
+                        traces: Optional[Sequence[Trace]] = None, device: int = 0) -> List[float]:
+    """One-call form on the reference's default workload (parse_workload() defaults,
+    benchmarks/parser.py:117-122: gpu_models_filtered.csv x openb_pod_list_default.csv)."""
+    cluster = cluster or ClusterSpec.load("gpu16")
+    traces = traces or [Trace.load("default")]
+    return BatchEvaluator(cluster, traces, device).evaluate_population(codes)

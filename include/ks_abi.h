@@ -1,0 +1,139 @@
+// ks_abi.h -- structures shared by the host library, the episode-replay kernel and the
+// NVRTC-compiled policy functions.  Plain C layout, no CUDA types, so the same file is
+// given to NVRTC as an in-memory header.
+//
+// Vocabulary follows the reference: pods, nodes, GPUs, episodes (one episode = one
+// (policy, trace) replay = one KubernetesSimulator.run_schedule(), simulator/main.py:50-72).
+#ifndef KS_ABI_H_
+#define KS_ABI_H_
+
+// ---- per-episode status words (SURVEY.md section 8b error convention) --------------------
+#define KS_ST_OK 0                // episode ran to the end of the event heap
+#define KS_ST_POLICY_EXCEPTION 1  // the policy raised (ZeroDivisionError, OverflowError ...)
+#define KS_ST_GPU_SHORTFALL 2     // ValueError("Not enough GPUs available"), simulator/main.py:164-165
+#define KS_ST_STEP_BUDGET 3       // caller-supplied event budget exhausted (the reference has none)
+#define KS_ST_UNSUPPORTED 4       // policy left the supported subset at run time (int64 overflow, complex ...)
+#define KS_ST_CAPACITY 5          // a per-slot scratch capacity was exceeded
+
+// ---- what a policy function returns instead of a score when it cannot -----------------
+// Scores handed to the simulator are int(max(0, score)) >= 0 (funsearch_integration.py:96),
+// so negative values are free to carry the exception channel.
+#define KS_RET_EXCEPTION (-1LL)
+#define KS_RET_UNSUPPORTED (-2LL)
+
+// ---- event-heap entry: (time:39 | id_rank:23 | is_deletion:1) -------------------------
+// Order of two entries == order of the reference's (time, Event) tuples: time first, then the
+// pod_id string order (event_simulator.py:16-17) which the host pre-computes as id_rank.
+// At most one event per pod is ever queued, so the low bit never decides a comparison.
+#define KS_RANK_BITS 23
+#define KS_KEY_SHIFT (KS_RANK_BITS + 1)
+#define KS_MAX_PODS (1 << KS_RANK_BITS)
+#define KS_MAX_TIME ((1LL << 39) - 2)
+#define KS_HEAP_INF 0xFFFFFFFFFFFFFFFFull
+
+// ---- placement record: (final creation time:40 | node:16 | gpu mask:8) -----------------
+#define KS_NODE_NONE 0xFFFFu     // never attempted / never placed
+#define KS_NODE_WAITING 0xFFFEu  // failed at least once and not placed (member of waiting_pods)
+#define KS_MAX_NODES 0xFFF0
+#define KS_MAX_GPUS_PER_NODE 8
+
+// ---- mutable per-node state, structure-of-arrays with stride n_pad (ints) ---------------
+#define KS_NS_CPU_LEFT 0
+#define KS_NS_MEM_LEFT 1
+#define KS_NS_GPU_LEFT 2
+#define KS_NS_GPU_MILLI_LEFT 3  // .. +7
+#define KS_NS_FIELDS 11
+
+// ---- constant per-node data, structure-of-arrays with stride n_pad (ints) ---------------
+#define KS_NC_CPU_TOTAL 0
+#define KS_NC_MEM_TOTAL 1
+#define KS_NC_NUM_GPUS 2
+#define KS_NC_GPU_MILLI_TOTAL 3  // .. +7
+#define KS_NC_GPU_MEM_TOTAL 11   // .. +7   (GPU.memory_mib_total == memory_mib_left: never mutated)
+#define KS_NC_FIELDS 19
+
+// ---- packed pod record, indexed by id_rank, 32 bytes -------------------------------------
+#define KS_POD_CPU 0
+#define KS_POD_MEM 1
+#define KS_POD_NUM_GPU 2
+#define KS_POD_GPU_MILLI 3
+#define KS_POD_DUR_LO 4
+#define KS_POD_DUR_HI 5
+#define KS_POD_ORIG_INDEX 6
+#define KS_POD_RESERVED 7
+#define KS_POD_INTS 8
+
+// What a policy sees of the pod being scheduled (entities.py:30-43); lives in shared memory,
+// identical for all lanes of the episode.
+struct KsPod {
+  int cpu_milli;
+  int memory_mib;
+  int num_gpu;
+  int gpu_milli;
+  long long creation_time;  // the retry-mutated value == time of the creation event being handled
+  long long duration_time;
+};
+
+// One trace resident in HBM.
+struct KsTraceDev {
+  const int* podrec;                  // [n_pods * KS_POD_INTS], indexed by id_rank
+  const unsigned long long* heap0;    // [n_pods] heapified creation events (event_simulator.py:23-34)
+  const unsigned long long* place0;   // [n_pods] initial placement records (orig creation time, NONE, 0)
+  long long n_pods;
+};
+
+// Per-episode output, 128 bytes.  Mirrors EvaluationResults (evaluator.py:16-25) plus counters.
+struct KsResult {
+  int status;
+  int placed;
+  int num_snapshots;
+  int num_fragmentation_events;
+  int max_nodes;
+  int max_waiting;
+  long long events;
+  long long attempts;
+  long long last_event_time;
+  double avg_cpu_utilization;
+  double avg_memory_utilization;
+  double avg_gpu_count_utilization;
+  double avg_gpu_memory_utilization;
+  double gpu_fragmentation_score;
+  double policy_score;  // evaluator.py:101-127, 0 when status != OK
+  long long scorer_calls;
+  long long device_cycles;  // clock64() span of the episode on its SM (diagnostic)
+  long long reserved[2];
+};
+
+// Kernel argument block.
+struct KsLaunch {
+  const KsTraceDev* traces;
+  const int* ep_policy;  // [n_episodes] slot in the linked policy table
+  const int* ep_trace;   // [n_episodes]
+  const int* nconst;     // [KS_NC_FIELDS * n_pad]
+  int* work_counter;     // zeroed by the host before launch; episodes are pulled in table order
+  KsResult* results;     // [n_episodes]
+  unsigned long long* placements;  // optional; episode e writes [place_off[e], +n_pods)
+  const long long* place_off;      // [n_episodes] or null
+  unsigned char* scratch;          // per resident team: heap tail + (placements if not requested) + waiting tail
+  long long scratch_per_team;
+  long long scratch_place_off;  // byte offset of the placement records inside a team's scratch (if not an output)
+  long long scratch_wait_off;   // byte offset of the waiting-list overflow inside a team's scratch
+  long long tot_cpu, tot_mem, tot_gpu_count, tot_gpu_milli;
+  long long max_events;  // 0 = unlimited
+  double snapshot_interval;
+  int n_episodes;
+  int n_nodes;
+  int n_pad;
+  int heap_smem_entries;  // heap[0, S) lives in shared memory, the rest in scratch
+  int wait_smem_entries;  // waiting list [0, W) in shared memory, the rest in scratch
+  int max_pods;           // largest n_pods over the traces of this batch (sizes the scratch regions)
+  int smem_per_team;      // bytes
+  int reserved;
+};
+
+#ifdef __cplusplus
+static_assert(sizeof(KsResult) == 128, "KsResult is 128 bytes");
+static_assert(sizeof(KsPod) == 32, "KsPod is 32 bytes");
+#endif
+
+#endif  // KS_ABI_H_

@@ -1,0 +1,135 @@
+/* ks_b200.h -- C ABI of libks_b200.so: the B200 (sm_100a) batched fitness evaluator that stands
+ * in for the reference's per-policy CPU replay.
+ *
+ * Every entry point is plain C: pointers and sizes only, no torch / CUDA-runtime types.  Device
+ * memory is owned by the caller (the Python host uses torch tensors and passes data_ptr());
+ * the library itself never allocates device memory.  All functions return 0 on success and a
+ * non-zero code otherwise; ks_last_error() then describes the failure (thread-local string).
+ *
+ * Each declaration cites the reference interface it replaces (paths relative to the reference
+ * repository ttanv/funsearch-kubernetes-simulator).
+ */
+#ifndef KS_B200_H_
+#define KS_B200_H_
+
+#include <stddef.h>
+
+#include "ks_abi.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define KS_API_VERSION 1
+
+/* Error text of the last failing call on this thread.  Replaces the Python exception text the
+ * reference's worker swallows (funsearch/funsearch_integration.py:63-64). */
+const char* ks_last_error(void);
+
+int ks_api_version(void);
+
+/* Bind the calling thread to `device` (its primary context, shared with torch) and load the CUDA
+ * driver.  Fails loudly when no driver / no sm_100 device is present: there is no CPU fallback.
+ * Replaces nothing in the reference (it has no device); precondition of everything below. */
+int ks_init(int device);
+
+/* ---- workload packing (host only, no GPU needed) ------------------------------------------ */
+
+/* Pack a pod list into the device layout: pod records indexed by id_rank, the heapified initial
+ * event heap and the initial placement image.
+ * Replaces: DiscreteEventSimulator.__init__/_populate_heap + heapq.heapify
+ * (simulator/event_simulator.py:23-34) over Pod objects (simulator/entities.py:30-43) produced by
+ * TraceParser.parse_pods (benchmarks/parser.py:68-101).
+ *   id_rank[i] = rank of pod i's pod_id in string order (Event.__lt__, event_simulator.py:16-17)
+ *   podrec  [n_pods * KS_POD_INTS] ints, heap0 [n_pods], place0 [n_pods]: caller-allocated host arrays */
+int ks_trace_pack(long long n_pods, const int* cpu_milli, const int* memory_mib, const int* num_gpu,
+                  const int* gpu_milli, const long long* creation_time, const long long* duration_time,
+                  const int* id_rank, int* podrec, unsigned long long* heap0, unsigned long long* place0);
+
+/* Pack a cluster into the constant node table (structure of arrays, stride n_pad = n_nodes rounded
+ * up to 32) and its evaluator totals {cpu, mem, gpu count, gpu milli}.
+ * Replaces: Cluster/Node/GPU objects (simulator/entities.py:4-26) from TraceParser.parse_nodes
+ * (benchmarks/parser.py:23-61) and SchedulingEvaluator.__init__'s totals (simulator/evaluator.py:35-38).
+ *   gpu_milli_total, gpu_mem_total: [n_nodes * 8] row-major, unused slots ignored
+ *   nconst: [KS_NC_FIELDS * n_pad] ints, totals: [4] */
+int ks_cluster_pack(int n_nodes, const int* cpu_total, const int* mem_total, const int* num_gpus,
+                    const int* gpu_milli_total, const int* gpu_mem_total, int* nconst, long long* totals);
+
+/* ---- policies --------------------------------------------------------------------------------- */
+
+/* Compile one policy, given as CUDA C source of a device function
+ *     extern "C" __device__ long long <symbol>(const KsPod*, const int* ns, int, const int* nc, int)
+ * (what the Python-AST translator emits), with NVRTC for sm_100a into a relocatable cubin.  Results
+ * are cached by source hash (in memory, and on disk when ks_set_cache_dir was called).
+ * Replaces: FunSearchScheduler._compile_policy, exec of the policy source
+ * (funsearch/funsearch_integration.py:77-89).  *policy receives a handle valid until ks_shutdown. */
+int ks_policy_compile(const char* cuda_source, const char* symbol, long long* policy);
+
+/* Same for n policies, compiled on `threads` host threads (0 = hardware concurrency).  status[i] is 0
+ * or the error code of policy i (its handle is then -1); the call itself fails only on bad arguments. */
+int ks_policy_compile_many(int n, const char* const* cuda_sources, const char* const* symbols, int threads,
+                           long long* policies, int* status);
+
+/* Log of the last failed compilation on this thread (NVRTC diagnostics). */
+const char* ks_compile_log(void);
+
+int ks_set_cache_dir(const char* path);
+
+/* Link the replay kernel with a table of policies (slot i of the table = policies[i]) and load the
+ * module on the current device.  Programs are cached by their policy list.
+ * Replaces: handing a scorer to KubernetesSimulator(..., scheduler=...) (simulator/main.py:29-41). */
+int ks_program_link(int n_policies, const long long* policies, long long* program);
+int ks_program_release(long long program);
+/* Link only (no device needed): proves every policy symbol resolves against the replay kernel. */
+int ks_program_link_check(int n_policies, const long long* policies, long long* linked_bytes);
+
+/* ---- evaluation ----------------------------------------------------------------------------- */
+
+/* Launch geometry and scratch requirement for a batch.  Fill n_episodes, n_nodes, max_pods,
+ * want_placements and (optionally, 0 = choose) teams_per_block / heap_smem_entries; the call fills the
+ * rest.  Purely arithmetic apart from reading the device's SM count and shared-memory limit. */
+typedef struct KsPlan {
+  int n_episodes;
+  int n_nodes;
+  int max_pods;
+  int want_placements;
+  int teams_per_block;   /* warps per CTA, one episode per warp */
+  int heap_smem_entries; /* event-heap entries kept in shared memory per team */
+  int wait_smem_entries;
+  int blocks;
+  int smem_per_team;
+  int smem_per_block;
+  long long scratch_per_team;
+  long long scratch_bytes; /* total device scratch the caller must provide (256-byte header included) */
+} KsPlan;
+int ks_plan(KsPlan* plan);
+
+/* One batch of episodes, everything already resident in device memory.
+ * Replaces: the ProcessPoolExecutor block over evaluate_policy_standalone
+ * (funsearch/funsearch_integration.py:30-64, 535-540), i.e. per episode
+ * KubernetesSimulator.run_schedule() (simulator/main.py:50-72) + SchedulingEvaluator
+ * (simulator/evaluator.py:27-164) + get_policy_score (:101-127). */
+typedef struct KsBatch {
+  const KsTraceDev* traces;       /* device: table of traces */
+  const int* ep_policy;           /* device [n_episodes]: slot in the program's policy table */
+  const int* ep_trace;            /* device [n_episodes] */
+  const int* nconst;              /* device: packed cluster (ks_cluster_pack) */
+  KsResult* results;              /* device [n_episodes] */
+  unsigned long long* placements; /* device, optional */
+  const long long* place_off;     /* device [n_episodes], required with placements */
+  void* scratch;                  /* device, plan.scratch_bytes, 256-byte aligned */
+  long long totals[4];            /* from ks_cluster_pack */
+  long long max_events;           /* 0 = no event budget (the reference has none) */
+  double snapshot_interval;       /* SchedulingEvaluator default 0.05 (evaluator.py:30) */
+} KsBatch;
+int ks_eval_batch(long long program, const KsPlan* plan, const KsBatch* batch, void* stream);
+
+/* Number of replay-kernel launches issued by this process so far (bench.py's gpu_launches). */
+long long ks_launch_count(void);
+
+int ks_shutdown(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* KS_B200_H_ */

@@ -1,0 +1,91 @@
+"""GPU parity: the CUDA replay (through the C ABI) against the committed golden fixtures recorded
+from the reference, and against the oracle on seeded inputs."""
+import pytest
+
+from helpers import assert_matches_golden, load_golden, specs_from_edge
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def env(built_lib):
+    from funsearch_kubernetes_simulator_b200 import ClusterSpec, Trace
+    from funsearch_kubernetes_simulator_b200.evaluator import BatchEvaluator
+    gold, pol = load_golden()
+    return dict(gold=gold, pol=pol, ClusterSpec=ClusterSpec, Trace=Trace, BatchEvaluator=BatchEvaluator)
+
+
+def _run_group(env, cluster, trace_names_to_trace, tags):
+    """tags: list of (tag, trace_name, policy_name); one launch for the whole group."""
+    names = list(trace_names_to_trace)
+    ev = env["BatchEvaluator"](cluster, [trace_names_to_trace[n] for n in names])
+    pnames = sorted({p for _, _, p in tags})
+    compiled = ev.compile([env["pol"][p] for p in pnames])
+    assert all(c is not None for c in compiled)
+    outs = ev.run_episodes(compiled, [pnames.index(p) for _, _, p in tags], [names.index(t) for _, t, _ in tags],
+                           want_placements=True)
+    for (tag, tname, _), out in zip(tags, outs):
+        assert_matches_golden(tag, env["gold"]["runs"][tag], out, trace_names_to_trace[tname], cluster)
+    return ev
+
+
+def test_default_trace_shipped_policies(env):
+    """BASELINE config 1: First-Fit, Best-Fit and the FunSearch champions on the bundled trace."""
+    cluster = env["ClusterSpec"].load("gpu16")
+    tr = env["Trace"].load("default")
+    tags = [(t, "default", t.split("|")[2]) for t in env["gold"]["runs"] if t.startswith("default|gpu16|")]
+    assert len(tags) >= 14
+    _run_group(env, cluster, {"default": tr}, tags)
+
+
+def test_all_bundled_traces_all_policies_one_launch(env):
+    cluster = env["ClusterSpec"].load("gpu16")
+    tags, traces = [], {}
+    for t in env["gold"]["runs"]:
+        parts = t.split("|")
+        if len(parts) == 3 and parts[1] == "gpu16" and not t.startswith("edge:"):
+            if parts[0] not in traces:
+                traces[parts[0]] = env["Trace"].load(parts[0])
+            tags.append((t, parts[0], parts[2]))
+    assert len(traces) == 19
+    _run_group(env, cluster, traces, tags)
+
+
+def test_1024_node_cluster(env):
+    cluster = env["ClusterSpec"].load("all1523").head(1024)
+    tr = env["Trace"].load("default")
+    tags = [(t, "default", t.split("|")[2]) for t in env["gold"]["runs"] if t.startswith("default|all1024|")]
+    assert tags
+    _run_group(env, cluster, {"default": tr}, tags)
+
+
+def test_64_node_cluster_prefix(env):
+    cluster = env["ClusterSpec"].load("gpu1213").head(64)
+    tr = env["Trace"].load("cpu300").head(4000)
+    tags = [(t, "x", t.split("|")[2]) for t in env["gold"]["runs"] if t.startswith("cpu300[:4000]|gpu64|")]
+    assert tags
+    _run_group(env, cluster, {"x": tr}, tags)
+
+
+def test_edge_cases(env):
+    for name, edge in env["gold"]["edge_cases"].items():
+        cluster, trace = specs_from_edge(edge)
+        tag = f"edge:{name}|{edge['policy']}"
+        _run_group(env, cluster, {"e": trace}, [(tag, "e", edge["policy"])])
+
+
+def test_heap_in_global_memory_gives_identical_results(env):
+    """The shared/global split of the event heap must not be observable."""
+    cluster = env["ClusterSpec"].load("gpu16")
+    tr = env["Trace"].load("default")
+    ev = env["BatchEvaluator"](cluster, [tr])
+    pn = ["ts_funsearch_4901", "ts_first_fit"]
+    compiled = ev.compile([env["pol"][p] for p in pn])
+    for S in (2, 64, 1024):
+        outs = ev.run_episodes(compiled, [0, 1], [0, 0], want_placements=True, heap_smem_entries=S)
+        assert ev.last_plan.heap_smem_entries == S
+        for p, out in zip(pn, outs):
+            assert_matches_golden(f"S={S} {p}", env["gold"]["runs"][f"default|gpu16|{p}"], out, tr, cluster)
+    outs = ev.run_episodes(compiled, [0, 1], [0, 0], want_placements=False)
+    for p, out in zip(pn, outs):
+        assert_matches_golden(f"no placements {p}", env["gold"]["runs"][f"default|gpu16|{p}"], out, tr, cluster)
