@@ -50,6 +50,17 @@ class KsBatch(C.Structure):
                 ("totals", C.c_longlong * 4), ("max_events", C.c_longlong), ("snapshot_interval", C.c_double)]
 
 
+class KsHostTrace(C.Structure):
+    _fields_ = [("podrec", C.c_void_p), ("heap0", C.c_void_p), ("place0", C.c_void_p), ("n_pods", C.c_longlong)]
+
+
+class KsHostBatch(C.Structure):
+    _fields_ = [("traces", C.POINTER(KsHostTrace)), ("n_traces", C.c_int), ("reserved", C.c_int),
+                ("ep_policy", C.c_void_p), ("ep_trace", C.c_void_p), ("nconst", C.c_void_p), ("results", C.c_void_p),
+                ("placements", C.c_void_p), ("place_off", C.c_void_p), ("placements_len", C.c_longlong),
+                ("totals", C.c_longlong * 4), ("max_events", C.c_longlong), ("snapshot_interval", C.c_double)]
+
+
 class KsError(RuntimeError):
     def __init__(self, code: int, message: str):
         super().__init__(f"libks_b200 error {code}: {message}")
@@ -74,6 +85,9 @@ _SIGNATURES = {
     "ks_program_release": (C.c_int, [C.c_longlong]),
     "ks_plan": (C.c_int, [C.POINTER(KsPlan)]),
     "ks_eval_batch": (C.c_int, [C.c_longlong, C.POINTER(KsPlan), C.POINTER(KsBatch), C.c_void_p]),
+    "ks_host_workspace_bytes": (C.c_int, [C.POINTER(KsPlan), C.POINTER(KsHostBatch), C.POINTER(C.c_longlong)]),
+    "ks_eval_batch_host": (C.c_int, [C.c_longlong, C.POINTER(KsPlan), C.POINTER(KsHostBatch), C.c_void_p, C.c_longlong,
+                                     C.c_void_p, C.POINTER(C.c_longlong), C.POINTER(C.c_longlong)]),
     "ks_launch_count": (C.c_longlong, []),
     "ks_shutdown": (C.c_int, []),
 }

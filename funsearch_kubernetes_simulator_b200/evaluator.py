@@ -233,6 +233,18 @@ class BatchEvaluator:
             out.append(oc)
         return out
 
+    # ------------------------------------------------------------------ resident form (inputs already in HBM)
+    def prepare_resident(self, policies: Sequence[CompiledPolicy], ep_policy: Sequence[int], ep_trace: Sequence[int],
+                         teams_per_block: int = 0, heap_smem_entries: int = 0) -> "ResidentBatch":
+        return ResidentBatch(self, policies, ep_policy, ep_trace, teams_per_block, heap_smem_entries)
+
+    # ------------------------------------------------------------------ host-buffer (end-to-end) form
+    def prepare_host_batch(self, policies: Sequence[CompiledPolicy], ep_policy: Sequence[int], ep_trace: Sequence[int],
+                           teams_per_block: int = 0, heap_smem_entries: int = 0) -> "HostBatch":
+        """Stage a batch in pinned host memory for ks_eval_batch_host (everything the step needs crosses
+        PCIe inside the call: traces, cluster table, episode table in; results out)."""
+        return HostBatch(self, policies, ep_policy, ep_trace, teams_per_block, heap_smem_entries)
+
     # ------------------------------------------------------------------ reference-shaped entry points
     def evaluate_population(self, codes: Sequence[str], trace_ids: Optional[Sequence[int]] = None) -> List[float]:
         """Fitness of every policy source of a generation: the batched replacement of the
@@ -271,6 +283,113 @@ class BatchEvaluator:
             return (idx, code, self.evaluate_population([code], [0])[0])
         except Exception:  # noqa: BLE001 -- the reference swallows everything into score 0
             return (idx, code, 0)
+
+
+class ResidentBatch:
+    """A batch whose episode table, result buffer and scratch already live in HBM: launch() is exactly one
+    ks_eval_batch call (one memset + one kernel), nothing else."""
+
+    def __init__(self, ev: BatchEvaluator, policies, ep_policy, ep_trace, teams_per_block=0, heap_smem_entries=0):
+        torch = ev._torch
+        self.ev = ev
+        self.n_ep = len(ep_policy)
+        self.prog = ev._program(tuple(int(p.handle) for p in policies))
+        pods_per_ep = [ev.traces[t].n_pods for t in ep_trace]
+        self.plan = ev.plan(self.n_ep, False, max(pods_per_ep), teams_per_block, heap_smem_entries)
+        self.d_pol = torch.from_numpy(np.ascontiguousarray(ep_policy, dtype=np.int32)).to(ev.device)
+        self.d_tr = torch.from_numpy(np.ascontiguousarray(ep_trace, dtype=np.int32)).to(ev.device)
+        self.d_res = torch.zeros(self.n_ep * nat.RESULT_DTYPE.itemsize, dtype=torch.uint8, device=ev.device)
+        self.d_scratch = torch.empty(int(self.plan.scratch_bytes), dtype=torch.uint8, device=ev.device)
+        b = nat.KsBatch()
+        b.traces = ev._trace_table.data_ptr()
+        b.ep_policy = self.d_pol.data_ptr()
+        b.ep_trace = self.d_tr.data_ptr()
+        b.nconst = ev._nconst.data_ptr()
+        b.results = self.d_res.data_ptr()
+        b.placements = None
+        b.place_off = None
+        b.scratch = self.d_scratch.data_ptr()
+        for k in range(4):
+            b.totals[k] = int(ev._totals[k])
+        b.max_events = 0
+        b.snapshot_interval = ev.snapshot_interval
+        self.batch = b
+
+    def launch(self, stream=None) -> None:
+        torch = self.ev._torch
+        st = stream or torch.cuda.current_stream(self.ev.device)
+        nat.check(self.ev.lib.ks_eval_batch(self.prog, C.byref(self.plan), C.byref(self.batch), C.c_void_p(st.cuda_stream)))
+
+    def results(self) -> np.ndarray:
+        return np.frombuffer(self.d_res.cpu().numpy().tobytes(), dtype=nat.RESULT_DTYPE)
+
+    def scores_tensor(self):
+        """Per-episode policy_score as a device fp64 tensor (a strided view of the result records)."""
+        torch = self.ev._torch
+        rec = self.d_res.view(torch.float64).view(self.n_ep, nat.RESULT_DTYPE.itemsize // 8)
+        return rec[:, nat.RESULT_DTYPE.fields["policy_score"][1] // 8]
+
+
+class HostBatch:
+    """One batch held in pinned host memory + a device workspace; run() = one ks_eval_batch_host call."""
+
+    def __init__(self, ev: BatchEvaluator, policies, ep_policy, ep_trace, teams_per_block=0, heap_smem_entries=0):
+        torch = ev._torch
+        self.ev = ev
+        self.n_ep = len(ep_policy)
+        self.prog = ev._program(tuple(int(p.handle) for p in policies))
+        pods_per_ep = [ev.traces[t].n_pods for t in ep_trace]
+        self.plan = ev.plan(self.n_ep, False, max(pods_per_ep), teams_per_block, heap_smem_entries)
+
+        def pinned(a: np.ndarray):
+            t = torch.from_numpy(np.ascontiguousarray(a)).pin_memory()
+            return t
+        self._keep = []
+        nconst, totals = ev.cluster.packed()
+        self.h_nconst = pinned(nconst)
+        self.h_pol = pinned(np.asarray(ep_policy, dtype=np.int32))
+        self.h_tr = pinned(np.asarray(ep_trace, dtype=np.int32))
+        self.h_res = torch.empty(self.n_ep * nat.RESULT_DTYPE.itemsize, dtype=torch.uint8).pin_memory()
+        self.h_traces = (nat.KsHostTrace * len(ev.traces))()
+        for i, tr in enumerate(ev.traces):
+            _r, podrec, heap0, place0 = tr.packed()
+            bufs = (pinned(podrec), pinned(heap0.view(np.int64)), pinned(place0.view(np.int64)))
+            self._keep.append(bufs)
+            self.h_traces[i].podrec = bufs[0].data_ptr()
+            self.h_traces[i].heap0 = bufs[1].data_ptr()
+            self.h_traces[i].place0 = bufs[2].data_ptr()
+            self.h_traces[i].n_pods = tr.n_pods
+        hb = nat.KsHostBatch()
+        hb.traces = self.h_traces
+        hb.n_traces = len(ev.traces)
+        hb.ep_policy = self.h_pol.data_ptr()
+        hb.ep_trace = self.h_tr.data_ptr()
+        hb.nconst = self.h_nconst.data_ptr()
+        hb.results = self.h_res.data_ptr()
+        hb.placements = None
+        hb.place_off = None
+        hb.placements_len = 0
+        for k in range(4):
+            hb.totals[k] = int(totals[k])
+        hb.max_events = 0
+        hb.snapshot_interval = ev.snapshot_interval
+        self.hb = hb
+        need = C.c_longlong(0)
+        nat.check(ev.lib.ks_host_workspace_bytes(C.byref(self.plan), C.byref(hb), C.byref(need)))
+        self.workspace = torch.empty(int(need.value), dtype=torch.uint8, device=ev.device)
+        self.h2d_bytes = 0
+        self.d2h_bytes = 0
+
+    def run(self, stream=None) -> np.ndarray:
+        """Host buffers in, host results out; returns the KsResult records (numpy structured array)."""
+        torch = self.ev._torch
+        st = stream or torch.cuda.current_stream(self.ev.device)
+        up, down = C.c_longlong(0), C.c_longlong(0)
+        nat.check(self.ev.lib.ks_eval_batch_host(self.prog, C.byref(self.plan), C.byref(self.hb),
+                                                 C.c_void_p(self.workspace.data_ptr()), self.workspace.numel(),
+                                                 C.c_void_p(st.cuda_stream), C.byref(up), C.byref(down)))
+        self.h2d_bytes, self.d2h_bytes = up.value, down.value
+        return np.frombuffer(self.h_res.numpy(), dtype=nat.RESULT_DTYPE)
 
 
 def evaluate_population(codes: Sequence[str], cluster: Optional[ClusterSpec] = None,

@@ -124,6 +124,38 @@ typedef struct KsBatch {
 } KsBatch;
 int ks_eval_batch(long long program, const KsPlan* plan, const KsBatch* batch, void* stream);
 
+/* The same evaluation with HOST buffers: the call copies the workload (traces, cluster, episode
+ * table) from host memory into the caller-provided device workspace, launches the replay kernel,
+ * copies the results (and placements, if requested) back and waits for the stream.  Use pinned host
+ * memory for truly asynchronous copies.  ks_host_workspace_bytes() tells how large the device
+ * workspace must be; *h2d_bytes / *d2h_bytes (optional) receive the bytes moved.
+ * Replaces, per call, what one pool worker of the reference does for every episode: parse_workload +
+ * deepcopy + run_schedule + get_policy_score (funsearch/funsearch_integration.py:36-59). */
+typedef struct KsHostTrace {
+  const int* podrec;                /* host, from ks_trace_pack */
+  const unsigned long long* heap0;  /* host */
+  const unsigned long long* place0; /* host */
+  long long n_pods;
+} KsHostTrace;
+typedef struct KsHostBatch {
+  const KsHostTrace* traces;
+  int n_traces;
+  int reserved;
+  const int* ep_policy;           /* host [n_episodes] */
+  const int* ep_trace;            /* host [n_episodes] */
+  const int* nconst;              /* host, from ks_cluster_pack */
+  KsResult* results;              /* host [n_episodes], out */
+  unsigned long long* placements; /* host, optional out: episode e at place_off[e] */
+  const long long* place_off;     /* host [n_episodes], even offsets */
+  long long placements_len;       /* entries in placements */
+  long long totals[4];
+  long long max_events;
+  double snapshot_interval;
+} KsHostBatch;
+int ks_host_workspace_bytes(const KsPlan* plan, const KsHostBatch* batch, long long* bytes);
+int ks_eval_batch_host(long long program, const KsPlan* plan, const KsHostBatch* batch, void* workspace,
+                       long long workspace_bytes, void* stream, long long* h2d_bytes, long long* d2h_bytes);
+
 /* Number of replay-kernel launches issued by this process so far (bench.py's gpu_launches). */
 long long ks_launch_count(void);
 

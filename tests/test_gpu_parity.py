@@ -89,3 +89,62 @@ def test_heap_in_global_memory_gives_identical_results(env):
     outs = ev.run_episodes(compiled, [0, 1], [0, 0], want_placements=False)
     for p, out in zip(pn, outs):
         assert_matches_golden(f"no placements {p}", env["gold"]["runs"][f"default|gpu16|{p}"], out, tr, cluster)
+
+
+def test_population_sample_against_oracle(env):
+    """Seeded inputs the goldens do not cover: 24 generated policy variants on a 2,500-pod prefix, compared
+    with the oracle run in this process (placement log, counters, metrics)."""
+    from helpers import oracle_specs, outcome_digest
+    from oracle import pysim
+    from funsearch_kubernetes_simulator_b200.variants import policy_population
+    cluster = env["ClusterSpec"].load("gpu16")
+    tr = env["Trace"].load("gpushare60").head(2500)
+    pop = policy_population(24, seed=11)
+    ev = env["BatchEvaluator"](cluster, [tr])
+    compiled = ev.compile(pop)
+    outs = ev.run_episodes(compiled, list(range(24)), [0] * 24, want_placements=True)
+    cs, ts = oracle_specs(cluster, tr)
+    for k, (src, out) in enumerate(zip(pop, outs)):
+        ref = pysim.run_episode(cs, ts, pysim.scorer_from_source(src))
+        assert (out.status, out.events, out.attempts, out.placed) == (ref.status, ref.events, ref.attempts, ref.placed), k
+        assert out.max_nodes == ref.max_nodes and out.max_waiting == ref.max_waiting, k
+        assert outcome_digest(tr, cluster, out) == pysim.placement_digest(ts, cs, ref), k
+        assert abs(out.policy_score - ref.score) <= 1e-9 * max(abs(ref.score), 1e-300), k
+
+
+def test_host_buffer_entry_point_matches_resident_path(env):
+    """ks_eval_batch_host (pinned host buffers) == ks_eval_batch (buffers resident in HBM)."""
+    import numpy as np
+    cluster = env["ClusterSpec"].load("gpu16")
+    tr = [env["Trace"].load("default").head(3000), env["Trace"].load("cpu100").head(1777)]
+    ev = env["BatchEvaluator"](cluster, tr)
+    pn = ["ts_funsearch_4901", "ts_best_fit", "fs_gpu_aware"]
+    compiled = ev.compile([env["pol"][p] for p in pn])
+    ep_pol, ep_tr = [0, 1, 2, 0, 1, 2], [0, 0, 0, 1, 1, 1]
+    rb = ev.prepare_resident(compiled, ep_pol, ep_tr)
+    rb.launch()
+    a = rb.results()
+    hb = ev.prepare_host_batch(compiled, ep_pol, ep_tr)
+    b = hb.run()
+    assert hb.h2d_bytes > 0 and hb.d2h_bytes == 6 * 128
+    for f in a.dtype.names:
+        if f not in ("device_cycles", "reserved"):
+            assert np.array_equal(a[f], b[f]), f
+    outs = ev.run_episodes(compiled, ep_pol, ep_tr)
+    assert [o.events for o in outs] == a["events"].tolist()
+
+
+def test_evaluate_population_reference_shaped_api(env):
+    """evaluate_population / evaluate_policy_standalone: scores as the reference's worker returns them,
+    0 for policies that raise or do not translate (funsearch_integration.py:63-64)."""
+    cluster = env["ClusterSpec"].load("gpu16")
+    tr = env["Trace"].load("default")
+    ev = env["BatchEvaluator"](cluster, [tr])
+    codes = [env["pol"]["ts_first_fit"], env["pol"]["ts_best_fit"], "def priority_function(pod, node):\n    return 1 / 0\n",
+             "def priority_function(pod, node):\n    import os\n    return 1\n", "this is not python"]
+    scores = ev.evaluate_population(codes)
+    want = [float.fromhex(env["gold"]["runs"][f"default|gpu16|{p}"]["score"]) for p in ("ts_first_fit", "ts_best_fit")]
+    assert abs(scores[0] - want[0]) < 1e-12 and abs(scores[1] - want[1]) < 1e-12
+    assert scores[2:] == [0.0, 0.0, 0.0]
+    idx, code, s = ev.evaluate_policy_standalone((7, codes[1]))
+    assert idx == 7 and code == codes[1] and abs(s - want[1]) < 1e-12
