@@ -23,6 +23,7 @@ KS_NS_FIELDS = 11
 KS_NODE_NONE = 0xFFFF
 KS_NODE_WAITING = 0xFFFE
 KS_MAX_TIME = (1 << 39) - 2
+KS_STATIC_SCRATCH_BYTES = 32 << 20
 
 # struct KsResult, 128 bytes
 RESULT_DTYPE = np.dtype([
@@ -85,6 +86,7 @@ _SIGNATURES = {
     "ks_program_release": (C.c_int, [C.c_longlong]),
     "ks_plan": (C.c_int, [C.POINTER(KsPlan)]),
     "ks_eval_batch": (C.c_int, [C.c_longlong, C.POINTER(KsPlan), C.POINTER(KsBatch), C.c_void_p]),
+    "ks_eval_batch_static": (C.c_int, [C.c_longlong, C.POINTER(KsPlan), C.POINTER(KsBatch), C.c_void_p]),
     "ks_host_workspace_bytes": (C.c_int, [C.POINTER(KsPlan), C.POINTER(KsHostBatch), C.POINTER(C.c_longlong)]),
     "ks_eval_batch_host": (C.c_int, [C.c_longlong, C.POINTER(KsPlan), C.POINTER(KsHostBatch), C.c_void_p, C.c_longlong,
                                      C.c_void_p, C.POINTER(C.c_longlong), C.POINTER(C.c_longlong)]),

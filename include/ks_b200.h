@@ -124,6 +124,34 @@ typedef struct KsBatch {
 } KsBatch;
 int ks_eval_batch(long long program, const KsPlan* plan, const KsBatch* batch, void* stream);
 
+/* ks_eval_batch for hosts that must not allocate device memory for the kernel's temporaries.
+ * (No counterpart in the reference: its worker is plain CPython and has no device.)
+ *
+ * Who needs it: ks_eval_batch expects the caller to hand in `batch->scratch`, which in practice means
+ * one more device allocation sized by ks_plan.  Some embedders cannot make that allocation: a service
+ * that received its input/output buffers from another component and runs under a fixed device-memory
+ * budget, or a host whose rules forbid cudaMalloc after start-up because it synchronises the whole
+ * device and would stall batches in flight on other streams.  For them the library carries its own
+ * scratch: a file-scope `static __device__` array of KS_STATIC_SCRATCH_BYTES (32 MiB) per GPU that
+ * loads the library, held until the process exits.  This entry point uses that array instead of
+ * `batch->scratch` (which is ignored and may be null); inputs and outputs are still the caller's.
+ * It calls no cudaMalloc/cudaFree and no allocating library routine.
+ *
+ * Limit: plan->scratch_bytes must not exceed KS_STATIC_SCRATCH_BYTES, otherwise the call fails with a
+ * message stating both numbers.  A plan that is too large can be shrunk by lowering plan->blocks
+ * (fewer resident teams; the kernel pulls episodes from a queue, so any block count is correct) and
+ * setting plan->scratch_bytes = 256 + plan->scratch_per_team * plan->blocks * plan->teams_per_block.
+ *
+ * Set-up: the first call on each device looks up the array's device address (cudaGetSymbolAddress,
+ * with that device current) and remembers it; make that first call before any stream capture begins.
+ * Sharing: every call on a device uses the same array, which keeps the previous call's contents.  The
+ * work counter at its start is cleared on `stream` before each launch and the kernel rewrites every
+ * other byte it reads, so back-to-back calls on one stream are fine, but two calls that can overlap
+ * on the GPU (different streams, different threads) race on the array and must be serialised by the
+ * caller. */
+#define KS_STATIC_SCRATCH_BYTES (32ll << 20)
+int ks_eval_batch_static(long long program, const KsPlan* plan, const KsBatch* batch, void* stream);
+
 /* The same evaluation with HOST buffers: the call copies the workload (traces, cluster, episode
  * table) from host memory into the caller-provided device workspace, launches the replay kernel,
  * copies the results (and placements, if requested) back and waits for the stream.  Use pinned host
