@@ -24,6 +24,7 @@ KS_NODE_NONE = 0xFFFF
 KS_NODE_WAITING = 0xFFFE
 KS_MAX_TIME = (1 << 39) - 2
 KS_STATIC_SCRATCH_BYTES = 32 << 20
+KS_PF_PREFIX_HOISTED = 1
 
 # struct KsResult, 128 bytes
 RESULT_DTYPE = np.dtype([
@@ -77,9 +78,9 @@ _SIGNATURES = {
     "ks_init": (C.c_int, [C.c_int]),
     "ks_trace_pack": (C.c_int, [C.c_longlong] + [C.c_void_p] * 10),
     "ks_cluster_pack": (C.c_int, [C.c_int] + [C.c_void_p] * 7),
-    "ks_policy_compile": (C.c_int, [C.c_char_p, C.c_char_p, C.POINTER(C.c_longlong)]),
-    "ks_policy_compile_many": (C.c_int, [C.c_int, C.POINTER(C.c_char_p), C.POINTER(C.c_char_p), C.c_int,
-                                         C.POINTER(C.c_longlong), C.POINTER(C.c_int)]),
+    "ks_policy_compile": (C.c_int, [C.c_char_p, C.c_char_p, C.c_longlong, C.POINTER(C.c_longlong)]),
+    "ks_policy_compile_many": (C.c_int, [C.c_int, C.POINTER(C.c_char_p), C.POINTER(C.c_char_p), C.POINTER(C.c_longlong),
+                                         C.c_int, C.POINTER(C.c_longlong), C.POINTER(C.c_int)]),
     "ks_set_cache_dir": (C.c_int, [C.c_char_p]),
     "ks_program_link": (C.c_int, [C.c_int, C.POINTER(C.c_longlong), C.POINTER(C.c_longlong)]),
     "ks_program_link_check": (C.c_int, [C.c_int, C.POINTER(C.c_longlong), C.POINTER(C.c_longlong)]),

@@ -23,10 +23,13 @@ typedef unsigned long long ks_u64;
 
 #define KS_D __device__ __forceinline__
 
-#define KS_CHECK(st)                              \
-  do {                                            \
-    if (st) return (st) == 1 ? KS_RET_EXCEPTION : KS_RET_UNSUPPORTED; \
-  } while (0)
+// The status word is sticky and remembers the FIRST failure (1 = exception, 2 = unsupported): helpers
+// never trap or fault on bad operands, so a translated policy keeps computing and tests the word only
+// where it returns.  Any other outcome after a failure is unobservable: the episode is over.
+#define KS_RETURN(x) return (st ? (st == 1 ? KS_RET_EXCEPTION : KS_RET_UNSUPPORTED) : (long long)(x))
+__device__ __forceinline__ void ks_fail(int* st, int code) {
+  if (!*st) *st = code;
+}
 
 // Heavy libm-class routines live once in the kernel module (ks_sim_kernel.cu) and are linked in.
 extern "C" __device__ double ks_rt_pow(double x, double y);
@@ -38,34 +41,43 @@ extern "C" __device__ double ks_rt_tan(double x);
 extern "C" __device__ ks_int ks_rt_idiv(ks_int a, ks_int b);  // C truncating quotient, b != 0
 
 // ------------------------------------------------------------------------------- field access
-KS_D int ks_ns(const int* ns, int stride, int field) { return ns[field * stride]; }
+// mutable node state: a plain shared-memory load (not volatile: the state does not change while a policy
+// is being evaluated, so the compiler may merge repeated reads of one field)
+KS_D int ks_ns(unsigned ns, int nss, int field) {
+  int v;
+  asm("ld.shared.s32 %0, [%1];" : "=r"(v) : "r"(ns + (unsigned)(field * nss)));
+  return v;
+}
 KS_D int ks_nc(const int* nc, int stride, int field) { return __ldg(nc + field * stride); }
+// fp64 division, shared by every policy of the module (keeps the per-policy code small)
+extern "C" __device__ double ks_rt_ddiv(double a, double b);
+#define ks_div(a, b) ks_rt_ddiv((a), (b))
 
 // ------------------------------------------------------------------------------- int64 with overflow
 KS_D ks_int ks_iadd(ks_int a, ks_int b, int* st) {
   ks_int r = (ks_int)((ks_u64)a + (ks_u64)b);
-  if (((a ^ r) & (b ^ r)) < 0) *st = 2;
+  if (((a ^ r) & (b ^ r)) < 0) ks_fail(st, 2);
   return r;
 }
 KS_D ks_int ks_isub(ks_int a, ks_int b, int* st) {
   ks_int r = (ks_int)((ks_u64)a - (ks_u64)b);
-  if (((a ^ b) & (a ^ r)) < 0) *st = 2;
+  if (((a ^ b) & (a ^ r)) < 0) ks_fail(st, 2);
   return r;
 }
 KS_D ks_int ks_imul(ks_int a, ks_int b, int* st) {
   ks_int lo = (ks_int)((ks_u64)a * (ks_u64)b);
   ks_int hi = __mul64hi(a, b);
-  if (hi != (lo >> 63)) *st = 2;
+  if (hi != (lo >> 63)) ks_fail(st, 2);
   return lo;
 }
 KS_D ks_int ks_ineg(ks_int a, int* st) {
-  if (a == (ks_int)0x8000000000000000LL) *st = 2;
+  if (a == (ks_int)0x8000000000000000LL) ks_fail(st, 2);
   return -a;
 }
 KS_D ks_int ks_iabs(ks_int a, int* st) { return a < 0 ? ks_ineg(a, st) : a; }
 // Python floor division / modulo on ints: sign of the divisor, ZeroDivisionError on 0.
 KS_D ks_int ks_ifloordiv(ks_int a, ks_int b, int* st) {
-  if (b == 0) { *st = 1; return 0; }
+  if (b == 0) { ks_fail(st, 1); return 0; }
   if (b == -1) return ks_ineg(a, st);
   ks_int q = ks_rt_idiv(a, b);
   ks_int r = a - q * b;
@@ -73,7 +85,7 @@ KS_D ks_int ks_ifloordiv(ks_int a, ks_int b, int* st) {
   return q;
 }
 KS_D ks_int ks_imod(ks_int a, ks_int b, int* st) {
-  if (b == 0) { *st = 1; return 0; }
+  if (b == 0) { ks_fail(st, 1); return 0; }
   if (b == -1) return 0;
   ks_int q = ks_rt_idiv(a, b);
   ks_int r = a - q * b;
@@ -85,17 +97,17 @@ KS_D double ks_i2d(ks_int a) { return __ll2double_rn(a); }
 // int / int: CPython rounds the exact quotient once.  Below 2**53 both operands convert exactly and
 // the IEEE division is that single rounding; larger operands would need the long-division path.
 KS_D double ks_itruediv(ks_int a, ks_int b, int* st) {
-  if (b == 0) { *st = 1; return 0.0; }
+  if (b == 0) { ks_fail(st, 1); return 0.0; }
   const ks_int lim = 1LL << 53;
-  if (a > lim || a < -lim || b > lim || b < -lim) { *st = 2; return 0.0; }
-  return __ddiv_rn((double)a, (double)b);
+  if (a > lim || a < -lim || b > lim || b < -lim) { ks_fail(st, 2); return 0.0; }
+  return ks_div((double)a, (double)b);
 }
 // int ** non-negative int, exact.
 KS_D ks_int ks_ipow(ks_int base, ks_int e, int* st) {
   ks_int r = 1;
   if (base == 0 || base == 1) return e == 0 ? 1 : base;
   if (base == -1) return (e & 1) ? -1 : 1;
-  if (e > 63) { *st = 2; return 0; }
+  if (e > 63) { ks_fail(st, 2); return 0; }
   while (e > 0) {
     if (e & 1) r = ks_imul(r, base, st);
     e >>= 1;
@@ -107,12 +119,12 @@ KS_D ks_int ks_ipow(ks_int base, ks_int e, int* st) {
 
 // ------------------------------------------------------------------------------- float
 KS_D double ks_ftruediv(double a, double b, int* st) {
-  if (b == 0.0) { *st = 1; return 0.0; }
-  return __ddiv_rn(a, b);
+  if (b == 0.0) { ks_fail(st, 1); return 0.0; }
+  return ks_div(a, b);
 }
 // float % float (Objects/floatobject.c float_rem)
 KS_D double ks_fmod(double a, double b, int* st) {
-  if (b == 0.0) { *st = 1; return 0.0; }
+  if (b == 0.0) { ks_fail(st, 1); return 0.0; }
   double m = fmod(a, b);
   if (m != 0.0) {
     if ((b < 0.0) != (m < 0.0)) m += b;
@@ -123,9 +135,9 @@ KS_D double ks_fmod(double a, double b, int* st) {
 }
 // float // float (Objects/floatobject.c _float_div_mod + float_floor_div)
 KS_D double ks_ffloordiv(double a, double b, int* st) {
-  if (b == 0.0) { *st = 1; return 0.0; }
+  if (b == 0.0) { ks_fail(st, 1); return 0.0; }
   double m = fmod(a, b);
-  double div = __ddiv_rn(a - m, b);
+  double div = ks_div(a - m, b);
   if (m != 0.0) {
     if ((b < 0.0) != (m < 0.0)) div -= 1.0;
   }
@@ -134,117 +146,68 @@ KS_D double ks_ffloordiv(double a, double b, int* st) {
     fl = floor(div);
     if (div - fl > 0.5) fl += 1.0;
   } else {
-    fl = copysign(0.0, __ddiv_rn(a, b));
+    fl = copysign(0.0, ks_div(a, b));
   }
   return fl;
 }
-KS_D bool ks_is_odd_integer(double y) { return fmod(fabs(y), 2.0) == 1.0; }
-// float ** float (Objects/floatobject.c float_pow); complex results are outside the subset.
-KS_D double ks_fpow(double x, double y, int* st) {
-  if (y == 0.0) return 1.0;
-  if (isnan(x)) return x;
-  if (isnan(y)) return x == 1.0 ? 1.0 : y;
-  if (isinf(y)) {
-    double ax = fabs(x);
-    if (ax == 1.0) return 1.0;
-    return ((y > 0.0) == (ax > 1.0)) ? fabs(y) : 0.0;
+// float ** float and math.pow live once in the kernel module (csrc/ks_sim_kernel.cu): they return the
+// result, or a NaN with a reserved payload when CPython would raise (1) / the result is complex (2).
+#define KS_NAN_TAG 0x7ff8dead
+extern "C" __device__ double ks_rt_fpow(double x, double y);
+extern "C" __device__ double ks_rt_mpow(double x, double y);
+KS_D double ks_untag(double r, int* st) {
+  const long long b = __double_as_longlong(r);
+  if ((int)(b >> 32) == KS_NAN_TAG) {
+    ks_fail(st, (int)(b & 3));
+    return 0.0;
   }
-  if (isinf(x)) {
-    bool odd = ks_is_odd_integer(y);
-    if (y > 0.0) return odd ? x : fabs(x);
-    return odd ? copysign(0.0, x) : 0.0;
-  }
-  if (x == 0.0) {
-    if (y < 0.0) { *st = 1; return 0.0; }  // ZeroDivisionError
-    return ks_is_odd_integer(y) ? x : 0.0;
-  }
-  bool neg = false;
-  if (x < 0.0) {
-    if (y != floor(y)) { *st = 2; return 0.0; }  // complex result
-    neg = ks_is_odd_integer(y);
-    x = -x;
-  }
-  if (x == 1.0) return neg ? -1.0 : 1.0;
-  double r = ks_rt_pow(x, y);
-  if (isinf(r) || isnan(r)) { *st = 1; return 0.0; }  // OverflowError / ValueError
-  return neg ? -r : r;
+  return r;
 }
+KS_D double ks_fpow(double x, double y, int* st) { return ks_untag(ks_rt_fpow(x, y), st); }
 // int ** negative int goes through float pow (Objects/longobject.c long_pow -> float_pow)
 KS_D double ks_ipow_neg(ks_int a, ks_int b, int* st) { return ks_fpow(ks_i2d(a), ks_i2d(b), st); }
 
 // int(x) for float x: truncation; OverflowError on inf, ValueError on nan.
 KS_D ks_int ks_f2i(double x, int* st) {
-  if (isnan(x) || isinf(x)) { *st = 1; return 0; }
-  if (x >= 9223372036854775808.0 || x <= -9223372036854775808.0) { *st = 2; return 0; }
+  if (isnan(x) || isinf(x)) { ks_fail(st, 1); return 0; }
+  if (x >= 9223372036854775808.0 || x <= -9223372036854775808.0) { ks_fail(st, 2); return 0; }
   return (ks_int)x;  // cvt.rzi
 }
 // round(x) with one argument: half to even, result is an int.
 KS_D ks_int ks_fround(double x, int* st) {
-  if (isnan(x) || isinf(x)) { *st = 1; return 0; }
+  if (isnan(x) || isinf(x)) { ks_fail(st, 1); return 0; }
   double r = rint(x);
-  if (r >= 9223372036854775808.0 || r <= -9223372036854775808.0) { *st = 2; return 0; }
+  if (r >= 9223372036854775808.0 || r <= -9223372036854775808.0) { ks_fail(st, 2); return 0; }
   return (ks_int)r;
 }
 KS_D double ks_msqrt(double x, int* st) {
-  if (x < 0.0) { *st = 1; return 0.0; }  // ValueError: math domain error
+  if (x < 0.0) { ks_fail(st, 1); return 0.0; }  // ValueError: math domain error
   return __dsqrt_rn(x);
 }
 KS_D double ks_mlog(double x, int* st) {
   if (isnan(x)) return x;
-  if (x <= 0.0) { *st = 1; return 0.0; }
+  if (x <= 0.0) { ks_fail(st, 1); return 0.0; }
   return ks_rt_log(x);
 }
 KS_D double ks_mexp(double x, int* st) {
   if (isnan(x)) return x;
   double r = ks_rt_exp(x);
-  if (isinf(r) && !isinf(x)) { *st = 1; return 0.0; }  // OverflowError: math range error
+  if (isinf(r) && !isinf(x)) { ks_fail(st, 1); return 0.0; }  // OverflowError: math range error
   return r;
 }
 KS_D double ks_msin(double x, int* st) {
-  if (isinf(x)) { *st = 1; return 0.0; }
+  if (isinf(x)) { ks_fail(st, 1); return 0.0; }
   return ks_rt_sin(x);
 }
 KS_D double ks_mcos(double x, int* st) {
-  if (isinf(x)) { *st = 1; return 0.0; }
+  if (isinf(x)) { ks_fail(st, 1); return 0.0; }
   return ks_rt_cos(x);
 }
 KS_D double ks_mtan(double x, int* st) {
-  if (isinf(x)) { *st = 1; return 0.0; }
+  if (isinf(x)) { ks_fail(st, 1); return 0.0; }
   return ks_rt_tan(x);
 }
-// math.pow(x, y): libm pow with CPython's error mapping (Modules/mathmodule.c math_pow_impl)
-KS_D double ks_mpow(double x, double y, int* st) {
-  if (isnan(x)) return y == 0.0 ? 1.0 : x;
-  if (isnan(y)) return x == 1.0 ? 1.0 : y;
-  if (isinf(x) || isinf(y)) {
-    if (isinf(x)) {
-      bool odd = !isinf(y) && ks_is_odd_integer(y);
-      if (y > 0.0) return odd ? x : fabs(x);
-      if (y == 0.0) return 1.0;
-      return odd ? copysign(0.0, x) : 0.0;
-    }
-    double ax = fabs(x);
-    if (ax == 1.0) return 1.0;
-    if (y > 0.0 && ax > 1.0) return y;
-    if (y < 0.0 && ax < 1.0) return -y;
-    return 0.0;
-  }
-  if (y == 0.0) return 1.0;
-  if (x == 0.0) {
-    if (y < 0.0) { *st = 1; return 0.0; }  // ValueError
-    return ks_is_odd_integer(y) ? x : 0.0;
-  }
-  bool neg = false;
-  if (x < 0.0) {
-    if (y != floor(y)) { *st = 1; return 0.0; }  // ValueError: math domain error
-    neg = ks_is_odd_integer(y);
-    x = -x;
-  }
-  if (x == 1.0) return neg ? -1.0 : 1.0;
-  double r = ks_rt_pow(x, y);
-  if (isinf(r) || isnan(r)) { *st = 1; return 0.0; }
-  return neg ? -r : r;
-}
+KS_D double ks_mpow(double x, double y, int* st) { return ks_untag(ks_rt_mpow(x, y), st); }
 
 // ------------------------------------------------------------------------------- exact int <-> float order
 // Python compares an int with a float by value, never by converting the int with rounding.

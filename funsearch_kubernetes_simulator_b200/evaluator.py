@@ -123,9 +123,10 @@ class BatchEvaluator:
             n = len(cps)
             srcs = (C.c_char_p * n)(*[cp.cuda_source.encode() for cp in cps])
             syms = (C.c_char_p * n)(*[cp.symbol.encode() for cp in cps])
+            flags = (C.c_longlong * n)(*[cp.flags for cp in cps])
             handles = (C.c_longlong * n)()
             status = (C.c_int * n)()
-            nat.check(self.lib.ks_policy_compile_many(n, srcs, syms, threads, handles, status))
+            nat.check(self.lib.ks_policy_compile_many(n, srcs, syms, flags, threads, handles, status))
             for i, cp in enumerate(cps):
                 if status[i] != 0:
                     raise nat.KsError(status[i], "NVRTC rejected translated policy:\n" +

@@ -38,9 +38,8 @@ ALLOWED_BUILTINS = {"abs", "min", "max", "sum", "len", "range", "enumerate", "in
 MATH_FUNCS = {"sqrt", "log", "exp", "pow", "sin", "cos", "tan"}
 OPERATOR_FUNCS = {"add": ast.Add, "sub": ast.Sub, "mul": ast.Mult, "truediv": ast.Div, "mod": ast.Mod}
 
-POD_FIELDS = {"cpu_milli": ("pod->cpu_milli", 31), "memory_mib": ("pod->memory_mib", 31),
-              "num_gpu": ("pod->num_gpu", 5), "gpu_milli": ("pod->gpu_milli", 25),
-              "creation_time": ("pod->creation_time", 40), "duration_time": ("pod->duration_time", 40)}
+POD_FIELDS = {"cpu_milli": ("p_cpu", 31), "memory_mib": ("p_mem", 31), "num_gpu": ("p_ngpu", 5),
+              "gpu_milli": ("p_gmilli", 25), "creation_time": ("p_ctime", 40), "duration_time": ("p_dur", 40)}
 NODE_STATE = {"cpu_milli_left": "KS_NS_CPU_LEFT", "memory_mib_left": "KS_NS_MEM_LEFT", "gpu_left": "KS_NS_GPU_LEFT"}
 NODE_CONST = {"cpu_milli_total": "KS_NC_CPU_TOTAL", "memory_mib_total": "KS_NC_MEM_TOTAL"}
 GPU_FIELDS = {"gpu_milli_left": ("ns", "KS_NS_GPU_MILLI_LEFT"), "gpu_milli_total": ("nc", "KS_NC_GPU_MILLI_TOTAL"),
@@ -70,6 +69,7 @@ class CompiledPolicy:
     symbol: str
     handle: Optional[int] = None
     var_types: Dict[str, str] = field(default_factory=dict)
+    flags: int = 0   # KS_PF_* (include/ks_abi.h); bit 0: the template's feasibility prefix is evaluated by the kernel
 
 
 def _join(a: Optional[str], b: str) -> str:
@@ -99,7 +99,10 @@ class _Returned(Exception):
 
 class _Translator:
     def __init__(self, fn: ast.FunctionDef, consts: Dict[str, object], var_types: Dict[str, str],
-                 var_bits: Dict[str, int], flagged: set):
+                 var_bits: Dict[str, int], flagged: set, base_bits: Optional[Dict[str, int]] = None, skip: int = 0):
+        self.base_bits = dict(base_bits or {})  # bits of each int variable's non-additive assignments (input)
+        self.seen_base: Dict[str, int] = {}
+        self.skip = skip                        # leading statements handled by the kernel (hoisted prefix)
         self.fn = fn
         self.consts = consts
         self.var_types = dict(var_types)      # declared (joined) types, input of this pass
@@ -146,13 +149,14 @@ class _Translator:
         return Val(ty, name, bits=bits, const=const)
 
     def raise_exc(self):
-        self.emit("return KS_RET_EXCEPTION;")
+        self.emit("KS_RETURN(KS_RET_EXCEPTION);")
 
     def unsupported_rt(self):
-        self.emit("return KS_RET_UNSUPPORTED;")
+        self.emit("KS_RETURN(KS_RET_UNSUPPORTED);")
 
     def check_st(self):
-        self.emit("KS_CHECK(st);")
+        # the status word is sticky (ks_pyrt.cuh): it is tested where the function returns
+        pass
 
     def fail(self, node, msg):
         line = getattr(node, "lineno", "?")
@@ -240,7 +244,7 @@ class _Translator:
             if name not in self.defined:
                 self.need_flag.add(name)
                 if name in self.flagged:
-                    self.emit(f"if (!b_{name}) return KS_RET_EXCEPTION;  // UnboundLocalError")
+                    self.emit(f"if (!b_{name}) KS_RETURN(KS_RET_EXCEPTION);  // UnboundLocalError")
             return Val(ty, f"v_{name}", bits=self.var_bits.get(name, 64))
         if name in self.consts:
             return self.const_val(self.consts[name], node)
@@ -268,7 +272,7 @@ class _Translator:
             return Val(STATIC, items=[self.const_val(x, node) for x in c])
         self.fail(node, f"constant of type {type(c).__name__}")
 
-    def store(self, name: str, v: Val, node):
+    def store(self, name: str, v: Val, node, additive: bool = False):
         if v.ty in (STATIC, LAMBDA, NONE, STR, POD, NODE, GPUS, MODULE):
             if v.ty == GPUS:
                 v = self.gpus_to_list()
@@ -277,6 +281,9 @@ class _Translator:
                     self.fail(node, f"variable {name!r} of type {v.ty} must be assigned exactly once, at function level")
                 self.static_vars[name] = v
                 return
+        if not additive and v.ty in (INT, BOOL):
+            self.base_bits[name] = max(self.base_bits.get(name, 0), v.bits)
+            self.seen_base[name] = max(self.seen_base.get(name, 0), v.bits)
         prev = self.seen_types.get(name)
         self.seen_types[name] = _join(prev, v.ty)
         self.seen_bits[name] = max(self.seen_bits.get(name, 0), v.bits if v.ty in (INT, BOOL) else 0)
@@ -302,7 +309,7 @@ class _Translator:
             raise _Returned()
         arr, f = GPU_FIELDS[attr]
         if arr == "ns":
-            return self.tmp(INT, f"(ks_int)ns[({f} + {g.code}) * nss]", bits=25)
+            return self.tmp(INT, f"(ks_int)ks_ns(ns, nss, {f} + {g.code})", bits=25)
         return self.tmp(INT, f"(ks_int)ks_nc(nc, ncs, {f} + {g.code})", bits=31)
 
     def attribute(self, node: ast.Attribute) -> Val:
@@ -318,7 +325,7 @@ class _Translator:
             raise _Returned()
         if base.ty == NODE:
             if a in NODE_STATE:
-                return self.tmp(INT, f"(ks_int)ns[{NODE_STATE[a]} * nss]", bits=32)
+                return self.tmp(INT, f"(ks_int)ks_ns(ns, nss, {NODE_STATE[a]})", bits=32)
             if a in NODE_CONST:
                 return self.tmp(INT, f"(ks_int)ks_nc(nc, ncs, {NODE_CONST[a]})", bits=31)
             if a == "gpus":
@@ -339,6 +346,7 @@ class _Translator:
     def gpus_to_list(self) -> Val:
         name = self.new("L")
         self.emit(f"KsGpuList {name}; {name}.n = ngpus;")
+        self.emit("#pragma unroll 1")
         self.emit(f"for (int q = 0; q < KS_MAX_GPUS_PER_NODE; ++q) {name}.g[q] = (signed char)q;")
         return Val(GPULIST, name)
 
@@ -393,9 +401,9 @@ class _Translator:
             self.check_st()
             return v
         if isinstance(op, ast.Div):
-            self.emit(f"if ({b.code} == 0) return KS_RET_EXCEPTION;  // ZeroDivisionError")
+            self.emit(f"if ({b.code} == 0) KS_RETURN(KS_RET_EXCEPTION);  // ZeroDivisionError")
             if a.bits <= 53 and b.bits <= 53:
-                return self.tmp(FLOAT, f"__ddiv_rn((double){a.code}, (double){b.code})")
+                return self.tmp(FLOAT, f"ks_div((double){a.code}, (double){b.code})")
             v = self.tmp(FLOAT, f"ks_itruediv({a.code}, {b.code}, &st)")
             self.check_st()
             return v
@@ -640,30 +648,34 @@ class _Translator:
                 bits = max(args[0].bits, args[1].bits)
             if len(args) == 3:
                 step = args[2].code
-                self.emit(f"if ({step} == 0) return KS_RET_EXCEPTION;  // ValueError: range() arg 3 must not be zero")
+                self.emit(f"if ({step} == 0) KS_RETURN(KS_RET_EXCEPTION);  // ValueError: range() arg 3 must not be zero")
             i = self.new("i")
             self.uses_budget = True
+            self.emit("#pragma unroll 1")
             self.emit(f"for (ks_int {i} = {lo}; ({step}) > 0 ? {i} < {hi} : {i} > {hi}; {i} += {step}) {{")
             self.ind += 1
-            self.emit("if (--budget < 0) return KS_RET_UNSUPPORTED;")
+            self.emit("if (--budget < 0) KS_RETURN(KS_RET_UNSUPPORTED);")
             elem = Val(INT, i, bits=min(64, bits + 1))
             cnt = Val(INT, f"(({i} - ({lo})) / ({step}))", bits=min(64, bits + 1))
         else:
             src = self.expr(it_node)
             if src.ty == GPUS:
                 i = self.new("g")
+                self.emit("#pragma unroll 1")
                 self.emit(f"for (int {i} = 0; {i} < ngpus; ++{i}) {{")
                 self.ind += 1
                 elem = Val(GPU, i)
                 cnt = Val(INT, f"(ks_int){i}", bits=4)
             elif src.ty == GPULIST:
                 i = self.new("k")
+                self.emit("#pragma unroll 1")
                 self.emit(f"for (int {i} = 0; {i} < {src.code}.n; ++{i}) {{")
                 self.ind += 1
                 elem = self.tmp(GPU, f"(int){src.code}.g[{i}]")
                 cnt = Val(INT, f"(ks_int){i}", bits=4)
             elif src.ty in (ILIST, FLIST):
                 i = self.new("k")
+                self.emit("#pragma unroll 1")
                 self.emit(f"for (int {i} = 0; {i} < {src.code}.n; ++{i}) {{")
                 self.ind += 1
                 elem = self.tmp(INT if src.ty == ILIST else FLOAT, f"{src.code}.v[{i}]")
@@ -756,7 +768,7 @@ class _Translator:
 
             def add():
                 v = self.expr(node.elt)
-                self.emit(f"if ({name}.n >= KS_MAX_GPUS_PER_NODE) return KS_RET_UNSUPPORTED;")
+                self.emit(f"if ({name}.n >= KS_MAX_GPUS_PER_NODE) KS_RETURN(KS_RET_UNSUPPORTED);")
                 self.emit(f"{name}.g[{name}.n++] = (signed char){v.code};")
             self.comprehension_loop(node, add, node)
             return Val(GPULIST, name)
@@ -767,7 +779,7 @@ class _Translator:
 
             def add():
                 v = self.expr(node.elt)
-                self.emit(f"if ({name}.n >= KS_LIST_CAP) return KS_RET_UNSUPPORTED;")
+                self.emit(f"if ({name}.n >= KS_LIST_CAP) KS_RETURN(KS_RET_UNSUPPORTED);")
                 code = v.code if lty == FLIST else self.as_int(v).code
                 self.emit(f"{name}.v[{name}.n++] = {code};")
             self.comprehension_loop(node, add, node)
@@ -811,6 +823,7 @@ class _Translator:
             src = self.gpus_to_list()
         if src.ty == GPULIST:
             i = self.new("k")
+            self.emit("#pragma unroll 1")
             self.emit(f"for (int {i} = 0; {i} < {src.code}.n; ++{i}) {{")
             self.ind += 1
             try:
@@ -821,6 +834,7 @@ class _Translator:
             return
         if src.ty in (ILIST, FLIST):
             i = self.new("k")
+            self.emit("#pragma unroll 1")
             self.emit(f"for (int {i} = 0; {i} < {src.code}.n; ++{i}) {{")
             self.ind += 1
             try:
@@ -937,7 +951,7 @@ class _Translator:
         if "res" not in state:
             self.raise_exc()  # empty literal: ValueError
             raise _Returned()
-        self.emit(f"if (!{found}) return KS_RET_EXCEPTION;  // ValueError: empty sequence")
+        self.emit(f"if (!{found}) KS_RETURN(KS_RET_EXCEPTION);  // ValueError: empty sequence")
         return Val(state["ety"], state["res"], bits=state["bits"] if state["ety"] in (INT, BOOL) else 64)
 
     def apply_lambda(self, fn_node: ast.AST, args: List[Val], node) -> Val:
@@ -997,6 +1011,7 @@ class _Translator:
             if kty not in (INT, FLOAT):
                 self.fail(node, "sort key must be int or float")
             self.emit(f"{CTYPE[kty]} {kname}[{cap}];")
+            self.emit("#pragma unroll 1")
             self.emit(f"for (int {i} = 0; {i} < {out}.n; ++{i}) {{")
             self.ind += 1
             el = self.tmp(ety, f"{'(int)' if ety == GPU else ''}{out}.{arr}[{i}]")
@@ -1010,6 +1025,7 @@ class _Translator:
         a, b = self.new("a"), self.new("b")
         rev = self.truth(reverse) if reverse is not None else "0"
         kt, et = CTYPE[kty], CTYPE[ety] if lst.ty != GPULIST else "signed char"
+        self.emit("#pragma unroll 1")
         self.emit(f"for (int {a} = 1; {a} < {out}.n; ++{a}) {{")
         self.ind += 1
         if key is not None:
@@ -1225,7 +1241,9 @@ class _Translator:
             a, b, q = self.new("a"), self.new("b"), self.new("q")
             self.emit(f"{CTYPE[base.ty]} {out}; const int {a} = ks_slice_bound({lo}, {base.code}.n), "
                       f"{b} = ks_slice_bound({hi}, {base.code}.n);")
-            self.emit(f"{out}.n = 0; for (int {q} = {a}; {q} < {b}; ++{q}) {out}.{arr}[{out}.n++] = {base.code}.{arr}[{q}];")
+            self.emit(f"{out}.n = 0;")
+            self.emit("#pragma unroll 1")
+            self.emit(f"for (int {q} = {a}; {q} < {b}; ++{q}) {out}.{arr}[{out}.n++] = {base.code}.{arr}[{q}];")
             return Val(base.ty, out)
         idx = self.expr(sl)
         if idx.ty not in (INT, BOOL):
@@ -1249,7 +1267,7 @@ class _Translator:
                 self.emit(f"switch ({k.code}) {{")
                 for j, it in enumerate(base.items):
                     self.emit(f"  case {j}: {res} = {self.convert(it, rty)}; break;")
-                self.emit("  default: return KS_RET_EXCEPTION;  // IndexError")
+                self.emit("  default: KS_RETURN(KS_RET_EXCEPTION);  // IndexError")
                 self.emit("}")
                 return Val(rty, res, bits=max(it.bits for it in base.items) if rty in (INT, BOOL) else 64)
             k = int(idx.const)
@@ -1266,7 +1284,7 @@ class _Translator:
             raise _Returned()
         k = self.new("j")
         self.emit(f"ks_int {k} = {idx.code}; if ({k} < 0) {k} += {n};")
-        self.emit(f"if ({k} < 0 || {k} >= {n}) return KS_RET_EXCEPTION;  // IndexError")
+        self.emit(f"if ({k} < 0 || {k} >= {n}) KS_RETURN(KS_RET_EXCEPTION);  // IndexError")
         if base.ty == GPUS:
             return Val(GPU, f"(int){k}")
         if base.ty == GPULIST:
@@ -1363,11 +1381,11 @@ class _Translator:
                 return False
             v = self.expr(s.value)
             if v.ty in (INT, BOOL):
-                self.emit(f"return ks_wrap_i({self.as_int(v).code});")
+                self.emit(f"KS_RETURN(ks_wrap_i({self.as_int(v).code}));")
             elif v.ty == FLOAT:
-                self.emit(f"return ks_wrap_f({v.code});")
+                self.emit(f"KS_RETURN(ks_wrap_f({v.code}));")
             elif v.ty == NUM:
-                self.emit(f"return ks_wrap_n({v.code});")
+                self.emit(f"KS_RETURN(ks_wrap_n({v.code}));")
             else:
                 self.raise_exc()  # max(0, <list/None/...>): TypeError
             return False
@@ -1397,11 +1415,23 @@ class _Translator:
         if isinstance(s, ast.AugAssign):
             if not isinstance(s.target, ast.Name):
                 self.fail(s, "augmented assignment to an attribute or subscript")
-            cur = self.lookup(s.target.id, s)
+            name = s.target.id
+            cur = self.lookup(name, s)
             if cur.ty in CTYPE and cur.ty in NUMERIC:
                 cur = self.tmp(cur.ty, cur.code, bits=cur.bits)
             v = self.expr(s.value)
-            self.store(s.target.id, self.arith(s.op, cur, v, s), s)
+            self_ref = any(isinstance(n, ast.Name) and n.id == name for n in ast.walk(s.value))
+            if (isinstance(s.op, (ast.Add, ast.Sub)) and cur.ty in (INT, BOOL) and v.ty in (INT, BOOL) and not self_ref
+                    and not self.scopes):
+                # x += e with e independent of x: the function executes at most LOOP_BUDGET * 8**3 < 2**27 such
+                # updates, so |x| < 2**(max(bits of x's other assignments, bits of e) + 27): no overflow check
+                grown = max(self.base_bits.get(name, 0), v.bits) + 27
+                if grown <= 62:
+                    r = self.tmp(INT, f"{self.as_int(cur).code} {'+' if isinstance(s.op, ast.Add) else '-'} {self.as_int(v).code}",
+                                 bits=grown)
+                    self.store(name, r, s, additive=True)
+                    return True
+            self.store(name, self.arith(s.op, cur, v, s), s)
             return True
         if isinstance(s, ast.If):
             try:
@@ -1453,7 +1483,7 @@ class _Translator:
             self.uses_budget = True
             self.emit("for (;;) {")
             self.ind += 1
-            self.emit("if (--budget < 0) return KS_RET_UNSUPPORTED;")
+            self.emit("if (--budget < 0) KS_RETURN(KS_RET_UNSUPPORTED);")
             try:
                 c = self.expr(s.test)
                 self.emit(f"if (!{self.truth(c)}) break;")
@@ -1474,7 +1504,7 @@ class _Translator:
             self.fail(s, "import")
         if isinstance(s, ast.Assert):
             c = self.expr(s.test)
-            self.emit(f"if (!{self.truth(c)}) return KS_RET_EXCEPTION;  // AssertionError")
+            self.emit(f"if (!{self.truth(c)}) KS_RETURN(KS_RET_EXCEPTION);  // AssertionError")
             return True
         if isinstance(s, ast.Raise):
             self.raise_exc()
@@ -1482,7 +1512,7 @@ class _Translator:
         self.fail(s, f"statement {type(s).__name__}")
 
     def run(self) -> bool:
-        return self.block(self.fn.body)
+        return self.block(self.fn.body[self.skip:])
 
 
 def _module_constants(tree: ast.Module, fn: ast.FunctionDef) -> Dict[str, object]:
@@ -1502,6 +1532,86 @@ def _module_constants(tree: ast.Module, fn: ast.FunctionDef) -> Dict[str, object
             raise PolicyCompileError(f"line {s.lineno}: helper function {s.name!r} is not supported")
         raise PolicyCompileError(f"line {getattr(s, 'lineno', '?')}: unsupported module-level statement")
     return consts
+
+
+_PREFIX_SRC = """
+def priority_function(pod, node):
+    if (pod.cpu_milli > node.cpu_milli_left or
+        pod.memory_mib > node.memory_mib_left or
+        pod.num_gpu > node.gpu_left):
+        return 0
+
+    if pod.num_gpu > 0:
+        available_gpus = 0
+        for gpu in node.gpus:
+            if gpu.gpu_milli_left >= pod.gpu_milli:
+                available_gpus += 1
+        if available_gpus < pod.num_gpu:
+            return 0
+"""
+_PREFIX_DUMP = [ast.dump(st) for st in ast.parse(_PREFIX_SRC).body[0].body]
+
+
+class _Rename(ast.NodeTransformer):
+    def __init__(self, mapping):
+        self.mapping = mapping
+
+    def visit_Name(self, node):
+        return ast.copy_location(ast.Name(id=self.mapping.get(node.id, node.id), ctx=node.ctx), node)
+
+
+def _reads_outside_own_binding(stmts, names) -> bool:
+    """True if any of `names` is read in `stmts` other than inside a comprehension / lambda / for-loop that
+    binds it first."""
+    def visit(node, bound):
+        if isinstance(node, ast.Name):
+            return isinstance(node.ctx, ast.Load) and node.id in names and node.id not in bound
+        if isinstance(node, (ast.ListComp, ast.GeneratorExp, ast.SetComp, ast.DictComp)):
+            inner = set(bound)
+            for g in node.generators:
+                if visit(g.iter, inner):
+                    return True
+                inner |= {n.id for n in ast.walk(g.target) if isinstance(n, ast.Name)}
+                if any(visit(c, inner) for c in g.ifs):
+                    return True
+            elts = [node.elt] if hasattr(node, "elt") else [node.key, node.value]
+            return any(visit(e, inner) for e in elts)
+        if isinstance(node, ast.Lambda):
+            return visit(node.body, bound | {a.arg for a in node.args.args})
+        if isinstance(node, ast.For):
+            if visit(node.iter, bound):
+                return True
+            inner = bound | {n.id for n in ast.walk(node.target) if isinstance(n, ast.Name)}
+            # after the loop the name may be unbound again (zero iterations): only the body is covered
+            return any(visit(c, inner) for c in node.body) or any(visit(c, bound) for c in node.orelse)
+        return any(visit(c, bound) for c in ast.iter_child_nodes(node))
+    return any(visit(st, set()) for st in stmts)
+
+
+def _hoistable_prefix(fn: ast.FunctionDef) -> int:
+    """Number of leading statements (docstring included) that are exactly the reference template's
+    feasibility prefix (funsearch/safe_execution.py:204-216) and can be evaluated by the kernel instead."""
+    body = fn.body
+    k = 1 if body and isinstance(body[0], ast.Expr) and isinstance(getattr(body[0], "value", None), ast.Constant) else 0
+    if len(body) < k + 2 or len(fn.args.args) != 2:
+        return 0
+    pod, node = fn.args.args[0].arg, fn.args.args[1].arg
+    a, b = body[k], body[k + 1]
+    try:
+        cnt = b.body[0].targets[0].id
+        gpu = b.body[1].target.id
+    except (AttributeError, IndexError):
+        return 0
+    mapping = {pod: "pod", node: "node", cnt: "available_gpus", gpu: "gpu"}
+    if len(set(mapping)) != 4 or {cnt, gpu} & {"pod", "node"}:
+        return 0
+    ren = _Rename(mapping)
+    import copy
+    if [ast.dump(ren.visit(copy.deepcopy(x))) for x in (a, b)] != _PREFIX_DUMP:
+        return 0
+    if _reads_outside_own_binding(body[k + 2:], {cnt, gpu}):
+        return 0
+    return k + 2
 
 
 _CACHE: Dict[str, CompiledPolicy] = {}
@@ -1530,13 +1640,18 @@ def compile_policy(source: str) -> CompiledPolicy:
             raise PolicyCompileError(f"line {getattr(n, 'lineno', '?')}: {type(n).__name__} is not supported")
     consts = _module_constants(tree, fn)
 
+    skip = _hoistable_prefix(fn)
     var_types: Dict[str, str] = {}
     var_bits: Dict[str, int] = {}
+    base_bits: Dict[str, int] = {}
     flagged: set = set()
     tr = None
     for it in range(8):
-        tr = _Translator(fn, consts, var_types, var_bits, flagged)
+        tr = _Translator(fn, consts, var_types, var_bits, flagged, base_bits, skip)
         falls = tr.run()
+        new_base = dict(base_bits)
+        for k, b in tr.seen_base.items():
+            new_base[k] = max(new_base.get(k, 0), b)
         new_types = dict(var_types)
         for k, t in tr.var_types.items():
             new_types[k] = _join(new_types.get(k), t)
@@ -1547,16 +1662,15 @@ def compile_policy(source: str) -> CompiledPolicy:
                 nb = 64  # a loop-carried integer keeps growing: give up on the range and check at run time
             new_bits[k] = min(64, nb)
         new_flagged = flagged | tr.need_flag
-        if new_types == var_types and new_bits == var_bits and new_flagged == flagged:
+        if new_types == var_types and new_bits == var_bits and new_flagged == flagged and new_base == base_bits:
             break
-        var_types, var_bits, flagged = new_types, new_bits, new_flagged
+        var_types, var_bits, flagged, base_bits = new_types, new_bits, new_flagged, new_base
     else:
         raise PolicyCompileError("type inference did not converge")
 
     symbol = "ks_pol_" + digest[:20]
     out = [f"// translated from a priority_function(pod, node) source, sha256 {digest[:16]}",
-           f'extern "C" __device__ long long {symbol}(const KsPod* __restrict__ pod, const int* __restrict__ ns, int nss, '
-           "const int* __restrict__ nc, int ncs) {",
+           f'extern "C" __device__ long long {symbol}(KS_POLICY_PARAMS) {{',
            "  int st = 0; (void)st;",
            "  const int ngpus = ks_nc(nc, ncs, KS_NC_NUM_GPUS); (void)ngpus;"]
     if tr.uses_budget:
@@ -1572,8 +1686,8 @@ def compile_policy(source: str) -> CompiledPolicy:
             out.append(f"  int b_{name} = 0;")
     out.extend(tr.lines)
     if falls:
-        out.append("  return KS_RET_EXCEPTION;  // fell off the end: int(max(0, None)) raises TypeError")
+        out.append("  KS_RETURN(KS_RET_EXCEPTION);  // fell off the end: int(max(0, None)) raises TypeError")
     out.append("}")
-    cp = CompiledPolicy(source, "\n".join(out) + "\n", symbol, None, dict(tr.var_types))
+    cp = CompiledPolicy(source, "\n".join(out) + "\n", symbol, None, dict(tr.var_types), 1 if skip else 0)
     _CACHE[digest] = cp
     return cp

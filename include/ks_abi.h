@@ -63,15 +63,23 @@
 #define KS_POD_RESERVED 7
 #define KS_POD_INTS 8
 
-// What a policy sees of the pod being scheduled (entities.py:30-43); lives in shared memory,
-// identical for all lanes of the episode.
-struct KsPod {
-  int cpu_milli;
-  int memory_mib;
-  int num_gpu;
-  int gpu_milli;
-  long long creation_time;  // the retry-mutated value == time of the creation event being handled
-  long long duration_time;
+// ---- policy function ABI ---------------------------------------------------------------
+// One translated priority_function(pod, node).  The pod's fields (entities.py:30-43) travel in registers
+// (p_ctime is the retry-mutated creation_time == time of the creation event being handled); `ns` is the
+// SHARED-memory byte address of this node's first mutable field (field f at ns + f * nss), `nc` points
+// at this node's first constant field in global memory (field f at nc[f * ncs]).
+// Returns int(max(0, score)) >= 0, or KS_RET_EXCEPTION / KS_RET_UNSUPPORTED.
+#define KS_POLICY_PARAMS                                                                              \
+  int p_cpu, int p_mem, int p_ngpu, int p_gmilli, long long p_ctime, long long p_dur, unsigned ns, int nss, \
+      const int *__restrict__ nc, int ncs
+typedef long long (*ks_policy_fn)(KS_POLICY_PARAMS);
+// flags of a dispatch-table entry
+#define KS_PF_PREFIX_HOISTED 1  // the source began with the reference template's feasibility prefix
+                                // (funsearch/safe_execution.py:204-216); the kernel evaluates it, the
+                                // function holds only what follows and is called for feasible nodes only
+struct KsPolicyEntry {
+  ks_policy_fn fn;
+  long long flags;
 };
 
 // One trace resident in HBM.
@@ -133,7 +141,6 @@ struct KsLaunch {
 
 #ifdef __cplusplus
 static_assert(sizeof(KsResult) == 128, "KsResult is 128 bytes");
-static_assert(sizeof(KsPod) == 32, "KsPod is 32 bytes");
 #endif
 
 #endif  // KS_ABI_H_

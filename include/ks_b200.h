@@ -58,17 +58,18 @@ int ks_cluster_pack(int n_nodes, const int* cpu_total, const int* mem_total, con
 /* ---- policies --------------------------------------------------------------------------------- */
 
 /* Compile one policy, given as CUDA C source of a device function
- *     extern "C" __device__ long long <symbol>(const KsPod*, const int* ns, int, const int* nc, int)
- * (what the Python-AST translator emits), with NVRTC for sm_100a into a relocatable cubin.  Results
+ *     extern "C" __device__ long long <symbol>(KS_POLICY_PARAMS)          (include/ks_abi.h)
+ * (what the Python-AST translator emits), with NVRTC for sm_100a into a relocatable cubin.  `flags` are
+ * the KS_PF_* bits the dispatch table will carry for this function.  Results
  * are cached by source hash (in memory, and on disk when ks_set_cache_dir was called).
  * Replaces: FunSearchScheduler._compile_policy, exec of the policy source
  * (funsearch/funsearch_integration.py:77-89).  *policy receives a handle valid until ks_shutdown. */
-int ks_policy_compile(const char* cuda_source, const char* symbol, long long* policy);
+int ks_policy_compile(const char* cuda_source, const char* symbol, long long flags, long long* policy);
 
 /* Same for n policies, compiled on `threads` host threads (0 = hardware concurrency).  status[i] is 0
  * or the error code of policy i (its handle is then -1); the call itself fails only on bad arguments. */
-int ks_policy_compile_many(int n, const char* const* cuda_sources, const char* const* symbols, int threads,
-                           long long* policies, int* status);
+int ks_policy_compile_many(int n, const char* const* cuda_sources, const char* const* symbols, const long long* flags,
+                           int threads, long long* policies, int* status);
 
 /* Log of the last failed compilation on this thread (NVRTC diagnostics). */
 const char* ks_compile_log(void);

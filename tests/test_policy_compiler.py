@@ -16,23 +16,24 @@ def test_shipped_policies_translate_compile_and_link(built_lib):
     n = len(cps)
     srcs = (C.c_char_p * n)(*[c.cuda_source.encode() for c in cps])
     syms = (C.c_char_p * n)(*[c.symbol.encode() for c in cps])
+    flags = (C.c_longlong * n)(*[c.flags for c in cps])
     handles = (C.c_longlong * n)()
     status = (C.c_int * n)()
-    nat.check(nat.lib().ks_policy_compile_many(n, srcs, syms, 0, handles, status))
+    nat.check(nat.lib().ks_policy_compile_many(n, srcs, syms, flags, 0, handles, status))
     assert list(status) == [0] * n, nat.lib().ks_compile_log().decode()
     size = C.c_longlong(0)
     nat.check(nat.lib().ks_program_link_check(n, handles, C.byref(size)))
     assert size.value > 100000
     # cache: same source -> same handle, no recompilation
     again = C.c_longlong(-1)
-    nat.check(nat.lib().ks_policy_compile(cps[0].cuda_source.encode(), cps[0].symbol.encode(), C.byref(again)))
+    nat.check(nat.lib().ks_policy_compile(cps[0].cuda_source.encode(), cps[0].symbol.encode(), cps[0].flags, C.byref(again)))
     assert again.value == handles[0]
 
 
 def test_nvrtc_error_is_reported(built_lib):
     from funsearch_kubernetes_simulator_b200 import _native as nat
     h = C.c_longlong(0)
-    rc = nat.lib().ks_policy_compile(b'extern "C" __device__ long long bad(const KsPod* p) { return nope; }', b"bad", C.byref(h))
+    rc = nat.lib().ks_policy_compile(b'extern "C" __device__ long long bad(KS_POLICY_PARAMS) { return nope; }', b"bad", 0, C.byref(h))
     assert rc != 0 and h.value == -1
     assert b"nope" in nat.lib().ks_compile_log()
 
@@ -45,7 +46,20 @@ def test_static_types_of_the_champions():
     t = compile_policy(pol["ts_funsearch_4800"]).var_types
     assert t["viable_gpus"] == "gpulist" and t["gpu_eff"] == "float"
     src = compile_policy(pol["ts_funsearch_4816"]).cuda_source
-    assert "ks_fpow" in src and "__ddiv_rn" in src and "fma" not in src.lower()
+    assert "ks_fpow" in src and "ks_div" in src and "fma" not in src.lower()
+
+
+def test_template_prefix_is_hoisted_only_when_it_is_exactly_the_template():
+    from funsearch_kubernetes_simulator_b200.policy_compiler import compile_policy
+    _g, pol = load_golden()
+    assert compile_policy(pol["ts_funsearch_4901"]).flags == 1   # re-binds `gpu` in generator expressions only
+    assert compile_policy(pol["fs_first_fit"]).flags == 1
+    assert compile_policy(pol["x_ignores_gpu_milli"]).flags == 0
+    src = pol["fs_first_fit"]
+    assert compile_policy(src.replace("return 1000", "return 1000 + available_gpus")).flags == 0  # reads a prefix variable
+    assert compile_policy(src.replace("pod.cpu_milli > node.cpu_milli_left", "pod.cpu_milli >= node.cpu_milli_left")).flags == 0
+    renamed = src.replace("available_gpus", "n_ok").replace("gpu", "g").replace("g_milli", "gpu_milli").replace("num_g", "num_gpu").replace("node.gs", "node.gpus").replace("g_left", "gpu_left")
+    assert compile_policy(renamed).flags == 1
 
 
 @pytest.mark.parametrize("body", [
