@@ -82,6 +82,7 @@ _SIGNATURES = {
     "ks_policy_compile_many": (C.c_int, [C.c_int, C.POINTER(C.c_char_p), C.POINTER(C.c_char_p), C.POINTER(C.c_longlong),
                                          C.c_int, C.POINTER(C.c_longlong), C.POINTER(C.c_int)]),
     "ks_set_cache_dir": (C.c_int, [C.c_char_p]),
+    "ks_set_compile_batch": (C.c_int, [C.c_int]),
     "ks_program_link": (C.c_int, [C.c_int, C.POINTER(C.c_longlong), C.POINTER(C.c_longlong)]),
     "ks_program_link_check": (C.c_int, [C.c_int, C.POINTER(C.c_longlong), C.POINTER(C.c_longlong)]),
     "ks_program_release": (C.c_int, [C.c_longlong]),
