@@ -103,6 +103,7 @@ class BatchEvaluator:
         self._scratch = None
         self.last_plan = None
         self.last_kernel_ms = None
+        self.warps_per_team = 0   # 0 = planner's choice; set to force a team width
 
     # ------------------------------------------------------------------ policies
     def compile(self, sources: Sequence[str], threads: int = 0) -> List[Optional[CompiledPolicy]]:
@@ -149,8 +150,9 @@ class BatchEvaluator:
 
     # ------------------------------------------------------------------ evaluation
     def plan(self, n_episodes: int, want_placements: bool, max_pods: Optional[int] = None,
-             teams_per_block: int = 0, heap_smem_entries: int = 0) -> nat.KsPlan:
+             teams_per_block: int = 0, heap_smem_entries: int = 0, warps_per_team: int = 0) -> nat.KsPlan:
         p = nat.KsPlan()
+        p.warps_per_team = warps_per_team or self.warps_per_team
         p.n_episodes = n_episodes
         p.n_nodes = self.cluster.n_nodes
         p.max_pods = max_pods or self.max_pods

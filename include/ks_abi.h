@@ -136,7 +136,7 @@ struct KsLaunch {
   int wait_smem_entries;  // waiting list [0, W) in shared memory, the rest in scratch
   int max_pods;           // largest n_pods over the traces of this batch (sizes the scratch regions)
   int smem_per_team;      // bytes
-  int reserved;
+  int warps_per_team;     // warps cooperating on one episode (1 = warp per episode)
 };
 
 #ifdef __cplusplus

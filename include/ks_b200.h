@@ -91,14 +91,15 @@ int ks_program_link_check(int n_policies, const long long* policies, long long* 
 /* ---- evaluation ----------------------------------------------------------------------------- */
 
 /* Launch geometry and scratch requirement for a batch.  Fill n_episodes, n_nodes, max_pods,
- * want_placements and (optionally, 0 = choose) teams_per_block / heap_smem_entries; the call fills the
+ * want_placements and (optionally, 0 = choose) warps_per_team / teams_per_block / heap_smem_entries; the call fills the
  * rest.  Purely arithmetic apart from reading the device's SM count and shared-memory limit. */
 typedef struct KsPlan {
   int n_episodes;
   int n_nodes;
   int max_pods;
   int want_placements;
-  int teams_per_block;   /* warps per CTA, one episode per warp */
+  int warps_per_team;    /* warps replaying one episode together (0 = choose: 1 up to 64 nodes, else one lane per node) */
+  int teams_per_block;   /* episodes in flight per CTA */
   int heap_smem_entries; /* event-heap entries kept in shared memory per team */
   int wait_smem_entries;
   int blocks;

@@ -148,3 +148,38 @@ def test_evaluate_population_reference_shaped_api(env):
     assert scores[2:] == [0.0, 0.0, 0.0]
     idx, code, s = ev.evaluate_policy_standalone((7, codes[1]))
     assert idx == 7 and code == codes[1] and abs(s - want[1]) < 1e-12
+
+
+@pytest.mark.parametrize("width", [2, 4, 8, 16])
+def test_multi_warp_teams_give_identical_results(env, width):
+    """An episode replayed by a team of W warps (leader + helpers at a named barrier) must equal W = 1."""
+    # 16 nodes: most helper lanes own no node at all
+    cluster = env["ClusterSpec"].load("gpu16")
+    tr = env["Trace"].load("default")
+    ev = env["BatchEvaluator"](cluster, [tr])
+    ev.warps_per_team = width
+    pn = ["ts_funsearch_4901", "ts_first_fit", "fs_worst_fit", "x_ignores_capacity"]
+    compiled = ev.compile([env["pol"][p] for p in pn])
+    outs = ev.run_episodes(compiled, list(range(len(pn))), [0] * len(pn), want_placements=True)
+    assert ev.last_plan.warps_per_team == width
+    for p, out in zip(pn, outs):
+        assert_matches_golden(f"W={width} {p}", env["gold"]["runs"][f"default|gpu16|{p}"], out, tr, cluster)
+    # 1,024 nodes: every lane owns nodes
+    big = env["ClusterSpec"].load("all1523").head(1024)
+    ev = env["BatchEvaluator"](big, [tr])
+    ev.warps_per_team = width
+    pn = ["ts_best_fit", "ts_funsearch_4816"]
+    compiled = ev.compile([env["pol"][p] for p in pn])
+    outs = ev.run_episodes(compiled, [0, 1], [0, 0], want_placements=True)
+    for p, out in zip(pn, outs):
+        assert_matches_golden(f"W={width} 1024 nodes {p}", env["gold"]["runs"][f"default|all1024|{p}"], out, tr, big)
+    # 64 nodes with retries and a busy waiting list
+    c64 = env["ClusterSpec"].load("gpu1213").head(64)
+    tr2 = env["Trace"].load("cpu300").head(4000)
+    ev = env["BatchEvaluator"](c64, [tr2])
+    ev.warps_per_team = width
+    pn = ["ts_best_fit", "ts_funsearch_4901", "ts_funsearch_4800"]
+    compiled = ev.compile([env["pol"][p] for p in pn])
+    outs = ev.run_episodes(compiled, [0, 1, 2], [0, 0, 0], want_placements=True)
+    for p, out in zip(pn, outs):
+        assert_matches_golden(f"W={width} 64 nodes {p}", env["gold"]["runs"][f"cpu300[:4000]|gpu64|{p}"], out, tr2, c64)

@@ -162,12 +162,12 @@ def test_plan_arithmetic(built_lib):
     p = nat.KsPlan()
     p.n_episodes, p.n_nodes, p.max_pods, p.want_placements = 1024, 16, 8152, 0
     nat.check(nat.lib().ks_plan(C.byref(p)))
-    assert 1 <= p.teams_per_block <= 8 and p.blocks * p.teams_per_block >= 1024 or p.blocks == 148
+    assert p.warps_per_team == 1 and 1 <= p.teams_per_block <= 8 and (p.blocks * p.teams_per_block >= 1024 or p.blocks == 148)
     assert p.smem_per_block <= 232448 and p.heap_smem_entries % 2 == 0
     assert p.scratch_bytes >= 256 + p.blocks * p.teams_per_block * p.scratch_per_team
     q = nat.KsPlan()
     q.n_episodes, q.n_nodes, q.max_pods, q.want_placements = 3, 1024, 100, 1
     nat.check(nat.lib().ks_plan(C.byref(q)))
-    assert q.blocks == 3 and q.teams_per_block == 1 and q.heap_smem_entries == 100
+    assert q.blocks == 3 and q.teams_per_block == 1 and q.heap_smem_entries == 100 and q.warps_per_team == 16
     bad = nat.KsPlan()
     assert nat.lib().ks_plan(C.byref(bad)) != 0
