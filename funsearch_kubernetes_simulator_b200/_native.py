@@ -42,7 +42,7 @@ assert RESULT_DTYPE.itemsize == 128
 class KsPlan(C.Structure):
     _fields_ = [("n_episodes", C.c_int), ("n_nodes", C.c_int), ("max_pods", C.c_int), ("want_placements", C.c_int),
                 ("warps_per_team", C.c_int), ("teams_per_block", C.c_int), ("heap_smem_entries", C.c_int), ("wait_smem_entries", C.c_int),
-                ("blocks", C.c_int), ("smem_per_team", C.c_int), ("smem_per_block", C.c_int),
+                ("ctas_per_sm", C.c_int), ("blocks", C.c_int), ("smem_per_team", C.c_int), ("smem_per_block", C.c_int),
                 ("scratch_per_team", C.c_longlong), ("scratch_bytes", C.c_longlong)]
 
 

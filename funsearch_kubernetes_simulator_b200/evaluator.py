@@ -104,6 +104,7 @@ class BatchEvaluator:
         self.last_plan = None
         self.last_kernel_ms = None
         self.warps_per_team = 0   # 0 = planner's choice; set to force a team width
+        self.ctas_per_sm = 0      # 0 = planner's choice; 1 = latency kernel, 2 = dense (throughput) kernel
 
     # ------------------------------------------------------------------ policies
     def compile(self, sources: Sequence[str], threads: int = 0) -> List[Optional[CompiledPolicy]]:
@@ -153,6 +154,7 @@ class BatchEvaluator:
              teams_per_block: int = 0, heap_smem_entries: int = 0, warps_per_team: int = 0) -> nat.KsPlan:
         p = nat.KsPlan()
         p.warps_per_team = warps_per_team or self.warps_per_team
+        p.ctas_per_sm = self.ctas_per_sm
         p.n_episodes = n_episodes
         p.n_nodes = self.cluster.n_nodes
         p.max_pods = max_pods or self.max_pods

@@ -102,6 +102,7 @@ typedef struct KsPlan {
   int teams_per_block;   /* episodes in flight per CTA */
   int heap_smem_entries; /* event-heap entries kept in shared memory per team */
   int wait_smem_entries;
+  int ctas_per_sm;       /* 0 = choose; 2 = throughput variant of the kernel (128 registers, two CTAs per SM) */
   int blocks;
   int smem_per_team;
   int smem_per_block;

@@ -183,3 +183,86 @@ def test_multi_warp_teams_give_identical_results(env, width):
     outs = ev.run_episodes(compiled, [0, 1, 2], [0, 0, 0], want_placements=True)
     for p, out in zip(pn, outs):
         assert_matches_golden(f"W={width} 64 nodes {p}", env["gold"]["runs"][f"cpu300[:4000]|gpu64|{p}"], out, tr2, c64)
+
+
+def _compare_with_c_oracle(tag, cluster, trace, out, builtin, params=None):
+    from oracle import coracle
+    res, t, n, m = coracle.run(cluster, trace, builtin, params)
+    assert (out.status, out.events, out.attempts, out.placed) == (res.status, res.events, res.attempts, res.placed), tag
+    assert (out.max_nodes, out.max_waiting, out.last_event_time) == (res.max_nodes, res.max_waiting, res.last_event_time), tag
+    ns = out.results.num_snapshots if out.results else 0
+    assert ns == res.num_snapshots and (out.results.num_fragmentation_events if out.results else 0) == res.num_frag, tag
+    import numpy as np
+    assert np.array_equal(out.final_creation_time, t) and np.array_equal(out.node_index, n) and np.array_equal(out.gpu_mask, m), tag
+    for got, want in ((out.policy_score, res.score), (out.results.avg_cpu_utilization, res.avg_cpu),
+                      (out.results.gpu_fragmentation_score, res.fragmentation)):
+        assert abs(got - want) <= 1e-9 * max(abs(want), 1e-300), (tag, got, want)
+
+
+BUILTIN = {"ts_first_fit": "first_fit", "ts_best_fit": "best_fit", "ts_funsearch_4901": "funsearch_4901",
+           "ts_funsearch_4816": "funsearch_4816", "ts_funsearch_4800": "funsearch_4800", "fs_worst_fit": "worst_fit"}
+
+
+def test_config3_shape_100k_pods_1024_nodes(env):
+    """BASELINE config 3, scaled to what the C oracle replays in seconds: synthetic Alibaba-shaped trace on the
+    first 1,024 rows of the all-node list, heavy enough that retries occur."""
+    from funsearch_kubernetes_simulator_b200 import synthetic_trace
+    cluster = env["ClusterSpec"].load("all1523").head(1024)
+    trace = synthetic_trace(100000, seed=1, load_factor=1500.0)
+    ev = env["BatchEvaluator"](cluster, [trace])
+    names = list(BUILTIN)
+    compiled = ev.compile([env["pol"][p] for p in names])
+    outs = ev.run_episodes(compiled, list(range(len(names))), [0] * len(names), want_placements=True)
+    assert ev.last_plan.warps_per_team == 16
+    assert any(o.results.num_fragmentation_events > 1000 for o in outs)
+    for p, out in zip(names, outs):
+        _compare_with_c_oracle(p, cluster, trace, out, BUILTIN[p])
+
+
+def test_config3_full_size_1m_pods_1024_nodes(env):
+    """BASELINE config 3 at full size (1,000,000 pods x 1,024 nodes, load factor 200: the cluster just keeps
+    up under a packing policy): three shipped policies bit-exact against the C oracle, plus size-independent
+    invariants on generated policy variants (under an event budget: a spreading policy never catches up)."""
+    import threading
+    import numpy as np
+    from funsearch_kubernetes_simulator_b200 import synthetic_trace
+    from funsearch_kubernetes_simulator_b200.variants import policy_population
+    from oracle import coracle
+    P, BUDGET = 1000000, 4000000
+    cluster = env["ClusterSpec"].load("all1523").head(1024)
+    trace = synthetic_trace(P, seed=3, load_factor=200.0)
+    names = ["ts_first_fit", "ts_best_fit", "ts_funsearch_4816"]
+    ref = {}
+
+    def work(p):
+        ref[p] = coracle.run(cluster, trace, BUILTIN[p], max_events=BUDGET)   # ctypes releases the GIL
+    threads = [threading.Thread(target=work, args=(p,)) for p in names]
+    for th in threads:
+        th.start()
+    variants = policy_population(3, seed=21)
+    ev = env["BatchEvaluator"](cluster, [trace])
+    compiled = ev.compile([env["pol"][p] for p in names] + variants)
+    outs = ev.run_episodes(compiled, list(range(len(compiled))), [0] * len(compiled), want_placements=True, max_events=BUDGET)
+    for th in threads:
+        th.join()
+    for p, out in zip(names, outs):
+        res, t, n, m = ref[p]
+        assert res.status == 0 and res.placed == P, p
+        assert (out.status, out.events, out.attempts, out.placed) == (res.status, res.events, res.attempts, res.placed), p
+        assert np.array_equal(out.final_creation_time, t) and np.array_equal(out.node_index, n) and np.array_equal(out.gpu_mask, m), p
+        assert abs(out.policy_score - res.score) <= 1e-9 * max(abs(res.score), 1e-300), p
+    for k, out in enumerate(outs):
+        nf = out.results.num_fragmentation_events
+        assert out.status in (0, 3) and out.attempts == out.placed + nf, k
+        if out.status == 0:
+            assert out.events == out.attempts + out.placed and out.placed == P and (out.node_index >= 0).all(), k
+        else:
+            assert out.events == BUDGET and out.policy_score == 0.0, k
+        assert int((out.node_index >= 0).sum()) == out.placed, k
+        # snapshots: thresholds 0.05, 0.1, ... (fp64 accumulation) not above events / P
+        thr, cnt = 0.05, 0
+        while out.events / P >= thr:
+            cnt += 1
+            thr += 0.05
+        assert out.results.num_snapshots == cnt, k
+        assert 0.0 <= out.policy_score <= 1.0
