@@ -152,6 +152,8 @@ def run_reference(args):
 
 # --------------------------------------------------------------------------------------------- CUDA arm
 def run_b200(args):
+    if os.environ.get("NCCL_DEBUG", "").upper() in ("VERSION", ""):
+        os.environ["NCCL_DEBUG"] = "WARN"   # keep stdout to the one JSON line
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
@@ -186,9 +188,10 @@ def run_b200(args):
     ev = BatchEvaluator(cluster, [trace], device=local)
 
     t0 = time.perf_counter()
-    from funsearch_kubernetes_simulator_b200.policy_compiler import compile_policy
+    from funsearch_kubernetes_simulator_b200 import policy_compiler
+    policy_compiler._CACHE.clear()   # policy_population() already translated them once: time a cold translation
     for s in pop:
-        compile_policy(s)
+        policy_compiler.compile_policy(s)
     t_translate = time.perf_counter() - t0
     t0 = time.perf_counter()
     compiled = ev.compile(pop)
@@ -298,7 +301,7 @@ def run_b200(args):
         "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "int64+f64", "data": "bundled OpenB default trace; synthetic policy population (seeded, no LLM)",
         "config": {"workload": WORKLOAD, "episodes_per_gpu": N_EPISODES, "l2": "flushed between timed steps (256 MiB write)",
-                   "teams_per_block": rb.plan.teams_per_block, "blocks": rb.plan.blocks,
+                   "warps_per_team": rb.plan.warps_per_team, "teams_per_block": rb.plan.teams_per_block, "blocks": rb.plan.blocks,
                    "heap_smem_entries": rb.plan.heap_smem_entries, "smem_per_block": rb.plan.smem_per_block,
                    "parity_ok_episodes": ok},
         "policy_evals_per_sec": evals_all / (ms_per_step * 1e-3),

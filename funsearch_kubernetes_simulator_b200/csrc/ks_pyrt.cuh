@@ -51,7 +51,11 @@ KS_D int ks_ns(unsigned ns, int nss, int field) {
 KS_D int ks_nc(const int* nc, int stride, int field) { return __ldg(nc + field * stride); }
 // fp64 division, shared by every policy of the module (keeps the per-policy code small)
 extern "C" __device__ double ks_rt_ddiv(double a, double b);
+#ifdef KS_INLINE_DIV
+#define ks_div(a, b) __ddiv_rn((a), (b))
+#else
 #define ks_div(a, b) ks_rt_ddiv((a), (b))
+#endif
 
 // ------------------------------------------------------------------------------- int64 with overflow
 KS_D ks_int ks_iadd(ks_int a, ks_int b, int* st) {

@@ -81,7 +81,7 @@ def test_heap_in_global_memory_gives_identical_results(env):
     ev = env["BatchEvaluator"](cluster, [tr])
     pn = ["ts_funsearch_4901", "ts_first_fit"]
     compiled = ev.compile([env["pol"][p] for p in pn])
-    for S in (2, 64, 1024):
+    for S in (512, 1024, 8152):
         outs = ev.run_episodes(compiled, [0, 1], [0, 0], want_placements=True, heap_smem_entries=S)
         assert ev.last_plan.heap_smem_entries == S
         for p, out in zip(pn, outs):
@@ -266,3 +266,29 @@ def test_config3_full_size_1m_pods_1024_nodes(env):
             thr += 0.05
         assert out.results.num_snapshots == cnt, k
         assert 0.0 <= out.policy_score <= 1.0
+
+
+def test_object_protocol_facade(env):
+    """GpuKubernetesSimulator: the reference's run_schedule() protocol on entity objects (tests/test_simulator.py
+    scenario: known answer pod1->node2, pod2->node1 [0], pod3->node2, pod4->node1 [0,1])."""
+    from types import SimpleNamespace as NS
+    from funsearch_kubernetes_simulator_b200.integration import GpuKubernetesSimulator
+
+    def gpu():
+        return NS(memory_mib_left=8000, memory_mib_total=8000, gpu_milli_left=1000, gpu_milli_total=1000)
+    node1 = NS(node_id="node1", cpu_milli_left=8000, cpu_milli_total=8000, memory_mib_left=16000, memory_mib_total=16000,
+               gpu_left=2, gpus=[gpu(), gpu()])
+    node2 = NS(node_id="node2", cpu_milli_left=4000, cpu_milli_total=4000, memory_mib_left=8000, memory_mib_total=8000,
+               gpu_left=0, gpus=[])
+    cluster = NS(nodes_dict={"node1": node1, "node2": node2})
+    rows = [("pod1", 1000, 2000, 0, 0, 0, 10), ("pod2", 2000, 4000, 1, 500, 5, 15), ("pod3", 3000, 6000, 0, 0, 10, 8),
+            ("pod4", 1500, 3000, 2, 400, 15, 12)]
+    pods = [NS(pod_id=r[0], cpu_milli=r[1], memory_mib=r[2], num_gpu=r[3], gpu_milli=r[4], gpu_spec="", creation_time=r[5],
+               duration_time=r[6], assigned_node="", assigned_gpus=[]) for r in rows]
+    sim = GpuKubernetesSimulator(cluster, pods, env["pol"]["sim_int_best_fit"], validate_invariants=True)
+    sim.run_schedule()
+    assert [p.assigned_node for p in pods] == ["node2", "node1", "node2", "node1"]
+    assert [p.assigned_gpus for p in pods] == [[], [0], [], [0, 1]]
+    g = env["gold"]["runs"]["edge:test_simulator|sim_int_best_fit"]
+    assert abs(sim.get_policy_score() - float.fromhex(g["score"])) < 1e-12 and sim.max_nodes == g["max_nodes"]
+    assert sim.get_evaluation_results().num_snapshots == g["num_snapshots"]
