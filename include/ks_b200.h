@@ -191,6 +191,11 @@ int ks_host_workspace_bytes(const KsPlan* plan, const KsHostBatch* batch, long l
 int ks_eval_batch_host(long long program, const KsPlan* plan, const KsHostBatch* batch, void* workspace,
                        long long workspace_bytes, void* stream, long long* h2d_bytes, long long* d2h_bytes);
 
+/* Test hook: out[i] = pow(x[i], y[i]) as the policies' `**` computes it on the device (glibc-2.39-exact fast
+ * path, see csrc/ks_glibc_pow.h).  Device pointers.  Replaces CPython's call into libm (Objects/floatobject.c
+ * float_pow), which is what makes `**` in a reference policy platform-specific. */
+int ks_debug_pow(long long program, const double* x, const double* y, double* out, int n, void* stream);
+
 /* Number of replay-kernel launches issued by this process so far (bench.py's gpu_launches). */
 long long ks_launch_count(void);
 

@@ -292,3 +292,31 @@ def test_object_protocol_facade(env):
     g = env["gold"]["runs"]["edge:test_simulator|sim_int_best_fit"]
     assert abs(sim.get_policy_score() - float.fromhex(g["score"])) < 1e-12 and sim.max_nodes == g["max_nodes"]
     assert sim.get_evaluation_results().num_snapshots == g["num_snapshots"]
+
+
+def test_device_pow_is_bit_identical_to_host_libm(env):
+    """`**` in a policy is libm pow() in CPython; the device must return the same bits (glibc-exact fast path).
+    The reference value is computed by this process's own libm, i.e. the GPU box's host: same image, same glibc."""
+    import ctypes as C
+    import math
+    import numpy as np
+    import torch
+    from funsearch_kubernetes_simulator_b200 import _native as nat
+    ev = env["BatchEvaluator"](env["ClusterSpec"].load("gpu16"), [env["Trace"].load("default").head(10)])
+    compiled = ev.compile([env["pol"]["ts_first_fit"]])
+    prog = ev._program((compiled[0].handle,))
+    rng = np.random.default_rng(12)
+    n = 400000
+    x = np.concatenate([rng.random(n // 4), np.exp((rng.random(n // 4) - 0.3) * 40.0),
+                        rng.integers(1, 2000000, n // 4).astype(np.float64), rng.random(n // 4) * 1000 + 1e-9])
+    ys = np.array([0.5, 0.6, 2.0, 2.5, 3.0, 1.5, 0.25, -1.0, -0.5, 1e-3, 7.0, 1 / 3])
+    y = np.concatenate([ys[rng.integers(0, 12, n // 4)], (rng.random(n // 4) - 0.5) * 20, ys[rng.integers(0, 12, n // 4)],
+                        rng.random(n // 4) * 4])
+    dx, dy = torch.from_numpy(x).cuda(), torch.from_numpy(y).cuda()
+    out = torch.empty_like(dx)
+    nat.check(nat.lib().ks_debug_pow(prog, C.c_void_p(dx.data_ptr()), C.c_void_p(dy.data_ptr()), C.c_void_p(out.data_ptr()),
+                                     n, C.c_void_p(torch.cuda.current_stream().cuda_stream)))
+    got = out.cpu().numpy()
+    want = np.array([math.pow(a, b) for a, b in zip(x.tolist(), y.tolist())])
+    bad = np.nonzero(got.view(np.uint64) != want.view(np.uint64))[0]
+    assert bad.size == 0, f"{bad.size} of {n} differ, e.g. x={x[bad[0]]!r} y={y[bad[0]]!r} got={got[bad[0]]!r} want={want[bad[0]]!r}"

@@ -1,0 +1,49 @@
+/* Validates csrc/ks_glibc_pow.h against the running libm: every operand pair inside the fast-path domain must
+ * give the bit pattern pow() gives.  gcc -O2 -ffp-contract=off tools/check_glibc_pow.c -lm && ./a.out [n] */
+#include <math.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+#define __device__
+static inline uint64_t bits_of(double d) { uint64_t u; memcpy(&u, &d, 8); return u; }
+static inline double dbl_of(uint64_t u) { double d; memcpy(&d, &u, 8); return d; }
+#define KS_PF_FMA(a, b, c) __builtin_fma((a), (b), (c))
+#define KS_PF_ADD(a, b) ((a) + (b))
+#define KS_PF_SUB(a, b) ((a) - (b))
+#define KS_PF_MUL(a, b) ((a) * (b))
+#define KS_PF_BITS(d) bits_of(d)
+#define KS_PF_DBL(u) dbl_of(u)
+#define KS_PF_I2D(i) ((double)(i))
+#define KS_PF_FN static inline
+#include "../funsearch_kubernetes_simulator_b200/csrc/ks_glibc_pow_tables.inc"
+#include "../funsearch_kubernetes_simulator_b200/csrc/ks_glibc_pow.h"
+
+static uint64_t rng = 88172645463325252ull;
+static uint64_t next(void) { rng ^= rng << 13; rng ^= rng >> 7; rng ^= rng << 17; return rng; }
+static double uni(void) { return (double)(next() >> 11) * (1.0 / 9007199254740992.0); }
+
+int main(int argc, char** argv) {
+  long n = argc > 1 ? atol(argv[1]) : 20000000, bad = 0, fast = 0;
+  const double ys[] = {0.5, 0.6, 2.0, 2.5, 3.0, 1.5, 0.25, -1.0, -0.5, 1e-3, 7.0, 0.3333333333333333};
+  for (long it = 0; it < n; ++it) {
+    double x, y;
+    switch (it & 3) {
+      case 0: x = uni(); y = ys[next() % 12]; break;                                   /* utilisations */
+      case 1: x = exp((uni() - 0.3) * 40.0); y = (uni() - 0.5) * 20.0; break;          /* wide range */
+      case 2: x = (double)(next() % 2000000 + 1); y = ys[next() % 12]; break;          /* integers (slack ** 0.6) */
+      default: x = uni() * 1000.0 + 1e-9; y = uni() * 4.0; break;
+    }
+    int ok;
+    double got = ks_glibc_pow_fast(x, y, &ok);
+    if (!ok) continue;
+    fast++;
+    double want = pow(x, y);
+    if (bits_of(got) != bits_of(want)) {
+      if (bad < 10) printf("MISMATCH x=%a y=%a got=%a want=%a\n", x, y, got, want);
+      bad++;
+    }
+  }
+  printf("checked %ld pairs, %ld on the fast path, %ld mismatches\n", n, fast, bad);
+  return bad != 0;
+}
