@@ -4,7 +4,7 @@ Drop-in for the reference's episode-evaluation path (simulator/main.py run_sched
 event_simulator.py + evaluator.py as driven by funsearch/funsearch_integration.py:30-64,535-540).
 """
 from .policy_compiler import CompiledPolicy, PolicyCompileError, compile_policy  # noqa: F401
-from .workload import ClusterSpec, Trace, available_traces, synthetic_trace  # noqa: F401
+from .workload import ClusterSpec, Trace, available_traces, bootstrap_trace, synthetic_trace  # noqa: F401
 
 
 def __getattr__(name):

@@ -170,6 +170,18 @@ def available_traces() -> list:
     return sorted(f[len("trace_"):-4] for f in os.listdir(DATA_DIR) if f.startswith("trace_") and f.endswith(".npz"))
 
 
+def bootstrap_trace(trace: Trace, seed: int) -> Trace:
+    """A seeded variant of `trace` (BASELINE config 4's "seeds": the simulator itself has no randomness, SURVEY.md
+    section 0): the arrival times and pod ids stay, the resource rows (cpu, mem, num_gpu, gpu_milli, duration) are
+    resampled with replacement from the trace's own rows.  seed 0 returns the trace unchanged."""
+    if seed == 0:
+        return trace
+    rng = np.random.Generator(np.random.PCG64(seed))
+    rows = rng.integers(0, trace.n_pods, size=trace.n_pods)
+    return Trace(trace.pod_ids, trace.cpu_milli[rows], trace.memory_mib[rows], trace.num_gpu[rows], trace.gpu_milli[rows],
+                 trace.creation_time, trace.duration_time[rows], f"{trace.name}#seed{seed}")
+
+
 def synthetic_trace(n_pods: int, seed: int = 0, base: Optional[Trace] = None, load_factor: float = 1.0,
                     name: Optional[str] = None) -> Trace:
     """Alibaba-shaped synthetic trace: rows (cpu, mem, num_gpu, gpu_milli,
