@@ -14,6 +14,7 @@ of libks_b200.so.  No CPU path exists: without the library or without a GPU the 
 from __future__ import annotations
 
 import ctypes as C
+import os
 from dataclasses import dataclass
 from typing import Iterable, List, Optional, Sequence, Tuple
 
@@ -107,9 +108,20 @@ class BatchEvaluator:
         self.ctas_per_sm = 0      # 0 = planner's choice; 1 = latency kernel, 2 = dense (throughput) kernel
 
     # ------------------------------------------------------------------ policies
-    def compile(self, sources: Sequence[str], threads: int = 0) -> List[Optional[CompiledPolicy]]:
-        """Python policy sources -> device functions (translate, then NVRTC in parallel).
-        A source outside the supported subset yields None (its episodes report status 'unsupported')."""
+    COMPILE_BATCH = 16          # policies per NVRTC program (ks_set_compile_batch)
+    POOL_THRESHOLD = 96         # fresh policies from which the process pool pays off
+
+    def compile(self, sources: Sequence[str], threads: int = 0, processes: Optional[int] = None) -> List[Optional[CompiledPolicy]]:
+        """Python policy sources -> device functions (translate, then NVRTC).
+        A source outside the supported subset yields None (its episodes report status 'unsupported').
+        Large batches of fresh policies are translated and compiled by a pool of `processes` worker processes
+        (default: the host's cores, at most 32; 0 disables) that share an on-disk cubin cache with this process."""
+        from . import policy_compiler
+        fresh = [s for s in dict.fromkeys(sources) if policy_compiler.cached(s) is None]
+        if processes is None:
+            processes = min(os.cpu_count() or 1, 32)
+        if processes > 1 and len(fresh) >= self.POOL_THRESHOLD:
+            self._compile_in_pool(fresh, processes)
         out: List[Optional[CompiledPolicy]] = []
         todo = []
         for src in sources:
@@ -138,6 +150,24 @@ class BatchEvaluator:
                 if cp.handle is None:
                     cp.handle = uniq[cp.symbol].handle
         return out
+
+    def _compile_in_pool(self, fresh: List[str], processes: int) -> None:
+        """Workers translate + NVRTC their slices into the shared disk cache; their translations are adopted here so
+        that the following in-process pass finds every group of COMPILE_BATCH policies already compiled."""
+        from . import compile_pool, policy_compiler
+        # slices are multiples of the NVRTC group size so that the parent re-forms identical groups
+        per = -(-len(fresh) // processes)
+        per = -(-per // self.COMPILE_BATCH) * self.COMPILE_BATCH
+        slices = [fresh[i:i + per] for i in range(0, len(fresh), per)]
+        cache_dir, results = compile_pool.compile_slices(slices, processes, self.COMPILE_BATCH)
+        nat.check(self.lib.ks_set_cache_dir(cache_dir.encode()))
+        nat.check(self.lib.ks_set_compile_batch(self.COMPILE_BATCH))
+        for sl, res in zip(slices, results):
+            if res is None:
+                continue  # that worker failed: these sources are translated and compiled in-process below
+            for src, r in zip(sl, res):
+                if r is not None:
+                    policy_compiler.adopt(src, *r)
 
     def _program(self, handles: Tuple[int, ...]) -> int:
         prog = self._programs.get(handles)

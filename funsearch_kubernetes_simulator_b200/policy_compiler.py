@@ -1617,6 +1617,21 @@ def _hoistable_prefix(fn: ast.FunctionDef) -> int:
 _CACHE: Dict[str, CompiledPolicy] = {}
 
 
+def cached(source: str) -> Optional[CompiledPolicy]:
+    """The translation of `source` if this process already has it."""
+    return _CACHE.get(hashlib.sha256(source.encode()).hexdigest())
+
+
+def adopt(source: str, cuda_source: str, symbol: str, flags: int) -> CompiledPolicy:
+    """Register a translation produced by another process (compile_pool) under this process's cache."""
+    digest = hashlib.sha256(source.encode()).hexdigest()
+    cp = _CACHE.get(digest)
+    if cp is None:
+        cp = CompiledPolicy(source, cuda_source, symbol, None, {}, flags)
+        _CACHE[digest] = cp
+    return cp
+
+
 def compile_policy(source: str) -> CompiledPolicy:
     """Translate a policy source to CUDA C.  Raises PolicyCompileError outside the subset; a
     SyntaxError in the source is reported the same way (the reference scores such a policy 0)."""
