@@ -268,6 +268,22 @@ class BatchEvaluator:
             out.append(oc)
         return out
 
+    # ------------------------------------------------------------------ test hook: raw scores of (pod, node) cases
+    def debug_scores(self, policies: Sequence[CompiledPolicy], slot: int, pods: np.ndarray, ns: np.ndarray, nc: np.ndarray) -> np.ndarray:
+        """Wrapped scores of policies[slot] for independent cases: pods [n, 6] int64, ns [KS_NS_FIELDS, n] int32,
+        nc [KS_NC_FIELDS, n] int32 (ks_debug_score).  -1 = the policy raised, -2 = left the supported subset."""
+        torch = self._torch
+        n = pods.shape[0]
+        prog = self._program(tuple(int(p.handle) for p in policies))
+        d_p = torch.from_numpy(np.ascontiguousarray(pods, dtype=np.int64)).to(self.device)
+        d_ns = torch.from_numpy(np.ascontiguousarray(ns, dtype=np.int32)).to(self.device)
+        d_nc = torch.from_numpy(np.ascontiguousarray(nc, dtype=np.int32)).to(self.device)
+        d_out = torch.empty(n, dtype=torch.int64, device=self.device)
+        st = torch.cuda.current_stream(self.device)
+        nat.check(self.lib.ks_debug_score(prog, slot, n, C.c_void_p(d_p.data_ptr()), C.c_void_p(d_ns.data_ptr()),
+                                          C.c_void_p(d_nc.data_ptr()), C.c_void_p(d_out.data_ptr()), C.c_void_p(st.cuda_stream)))
+        return d_out.cpu().numpy()
+
     # ------------------------------------------------------------------ resident form (inputs already in HBM)
     def prepare_resident(self, policies: Sequence[CompiledPolicy], ep_policy: Sequence[int], ep_trace: Sequence[int],
                          teams_per_block: int = 0, heap_smem_entries: int = 0) -> "ResidentBatch":

@@ -196,6 +196,14 @@ int ks_eval_batch_host(long long program, const KsPlan* plan, const KsHostBatch*
  * float_pow), which is what makes `**` in a reference policy platform-specific. */
 int ks_debug_pow(long long program, const double* x, const double* y, double* out, int n, void* stream);
 
+/* Test hook: the wrapped score int(max(0, priority_function(pod, node))) of policy-table slot `slot` for n independent
+ * (pod, node) cases, obtained exactly as the replay kernel obtains it; KS_RET_EXCEPTION / KS_RET_UNSUPPORTED where the policy
+ * raises / leaves the subset.  Replaces a direct call of FunSearchScheduler.__call__ (funsearch_integration.py:91-101).
+ * Device pointers: pods [n][6] int64 (cpu, mem, num_gpu, gpu_milli, creation_time, duration), ns [KS_NS_FIELDS][n],
+ * nc [KS_NC_FIELDS][n], out [n]. */
+int ks_debug_score(long long program, int slot, int n, const long long* pods, const int* ns, const int* nc, long long* out,
+                   void* stream);
+
 /* Number of replay-kernel launches issued by this process so far (bench.py's gpu_launches). */
 long long ks_launch_count(void);
 
