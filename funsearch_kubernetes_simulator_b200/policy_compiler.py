@@ -525,19 +525,26 @@ class _Translator:
         res = self.new("c")
         self.emit(f"int {res} = 0;")
         depth = 0
-        for i, (op, cmpn) in enumerate(zip(node.ops, node.comparators)):
-            right = self.expr(cmpn)
-            e = self.compare_pair(op, left, right, node)
-            if i == len(node.ops) - 1:
-                self.emit(f"{res} = {e};")
-            else:
-                self.emit(f"if ({e}) {{")
-                self.ind += 1
-                depth += 1
-            left = right
-        for _ in range(depth):
-            self.ind -= 1
-            self.emit("}")
+        try:
+            for i, (op, cmpn) in enumerate(zip(node.ops, node.comparators)):
+                try:
+                    right = self.expr(cmpn)
+                    e = self.compare_pair(op, left, right, node)
+                except _Returned:
+                    if i == 0:
+                        raise  # the first comparison always runs
+                    break      # later comparators are only evaluated while the chain holds
+                if i == len(node.ops) - 1:
+                    self.emit(f"{res} = {e};")
+                else:
+                    self.emit(f"if ({e}) {{")
+                    self.ind += 1
+                    depth += 1
+                left = right
+        finally:
+            for _ in range(depth):
+                self.ind -= 1
+                self.emit("}")
         return Val(BOOL, res, bits=1)
 
     # ------------------------------------------------------------------ boolean operators / conditionals
@@ -558,18 +565,25 @@ class _Translator:
         is_and = isinstance(node.op, ast.And)
         depth = 0
         bits = 0
-        for i, vn in enumerate(node.values):
-            v = self.expr(vn)
-            bits = max(bits, v.bits)
-            self.emit(f"{res} = {self.convert(v, rty)};")
-            if i < len(node.values) - 1:
-                cond = self.truth(Val(rty, res))
-                self.emit(f"if ({cond if is_and else '!' + cond}) {{")
-                self.ind += 1
-                depth += 1
-        for _ in range(depth):
-            self.ind -= 1
-            self.emit("}")
+        try:
+            for i, vn in enumerate(node.values):
+                try:
+                    v = self.expr(vn)
+                except _Returned:
+                    if i == 0:
+                        raise  # the first operand always runs: the whole expression always raises
+                    break      # a later operand raises only when evaluation gets that far: code after the expression stays reachable
+                bits = max(bits, v.bits)
+                self.emit(f"{res} = {self.convert(v, rty)};")
+                if i < len(node.values) - 1:
+                    cond = self.truth(Val(rty, res))
+                    self.emit(f"if ({cond if is_and else '!' + cond}) {{")
+                    self.ind += 1
+                    depth += 1
+        finally:
+            for _ in range(depth):
+                self.ind -= 1
+                self.emit("}")
         return Val(rty, res, bits=bits if rty in (INT, BOOL) else 64)
 
     def dry_type(self, node: ast.AST) -> str:
@@ -671,7 +685,7 @@ class _Translator:
                 self.emit("#pragma unroll 1")
                 self.emit(f"for (int {i} = 0; {i} < {src.code}.n; ++{i}) {{")
                 self.ind += 1
-                elem = self.tmp(GPU, f"(int){src.code}.g[{i}]")
+                elem = self.tmp(GPU, f"((int){src.code}.g[{i}] & 7)")
                 cnt = Val(INT, f"(ks_int){i}", bits=4)
             elif src.ty in (ILIST, FLIST):
                 i = self.new("k")
@@ -687,22 +701,28 @@ class _Translator:
                     self.ind += 1
                     if enum:
                         self.bind(idx_t, self.const_val(k, node), node)
-                    self.bind(target, item, node)
-                    # break/continue inside an unrolled literal loop are not representable
-                    body_fn(unrolled=True)
-                    self.ind -= 1
-                    self.emit("}")
+                    try:
+                        self.bind(target, item, node)
+                        # break/continue inside an unrolled literal loop are not representable
+                        body_fn(unrolled=True)
+                    except _Returned:
+                        pass  # conservative: what follows is translated as reachable
+                    finally:
+                        self.ind -= 1
+                        self.emit("}")
                 return
             else:
                 if src.ty in NUMERIC or src.ty in (NONE, GPU, POD, NODE):
                     self.raise_exc()  # TypeError: not iterable
                     raise _Returned()
                 self.fail(node, f"iteration over {src.ty}")
-        if enum:
-            self.bind(idx_t, self.tmp(INT, cnt.code, bits=cnt.bits), node)
-        self.bind(target, elem, node)
         try:
+            if enum:
+                self.bind(idx_t, self.tmp(INT, cnt.code, bits=cnt.bits), node)
+            self.bind(target, elem, node)
             body_fn(unrolled=False)
+        except _Returned:
+            pass  # the body raises, but the loop may run zero times: code after it stays reachable
         finally:
             self.ind -= 1
             self.emit("}")
@@ -827,7 +847,9 @@ class _Translator:
             self.emit(f"for (int {i} = 0; {i} < {src.code}.n; ++{i}) {{")
             self.ind += 1
             try:
-                fn(self.tmp(GPU, f"(int){src.code}.g[{i}]"))
+                fn(self.tmp(GPU, f"((int){src.code}.g[{i}] & 7)"))
+            except _Returned:
+                pass  # the list may be empty: code after the loop stays reachable
             finally:
                 self.ind -= 1
                 self.emit("}")
@@ -839,6 +861,8 @@ class _Translator:
             self.ind += 1
             try:
                 fn(self.tmp(INT if src.ty == ILIST else FLOAT, f"{src.code}.v[{i}]"))
+            except _Returned:
+                pass
             finally:
                 self.ind -= 1
                 self.emit("}")
@@ -1014,11 +1038,15 @@ class _Translator:
             self.emit("#pragma unroll 1")
             self.emit(f"for (int {i} = 0; {i} < {out}.n; ++{i}) {{")
             self.ind += 1
-            el = self.tmp(ety, f"{'(int)' if ety == GPU else ''}{out}.{arr}[{i}]")
-            kv = self.apply_lambda(key, [el], node)
-            self.emit(f"{kname}[{i}] = {self.convert(kv, kty) if kv.ty != BOOL else self.as_int(kv).code};")
-            self.ind -= 1
-            self.emit("}")
+            try:
+                el = self.tmp(ety, f"((int){out}.{arr}[{i}] & 7)" if ety == GPU else f"{out}.{arr}[{i}]")
+                kv = self.apply_lambda(key, [el], node)
+                self.emit(f"{kname}[{i}] = {self.convert(kv, kty) if kv.ty != BOOL else self.as_int(kv).code};")
+            except _Returned:
+                pass  # the key raises for every element, but the list may be empty
+            finally:
+                self.ind -= 1
+                self.emit("}")
         else:
             kty = ety
         # stable insertion sort (list.sort is stable; reverse=True keeps equal elements in original order)
@@ -1286,9 +1314,11 @@ class _Translator:
         self.emit(f"ks_int {k} = {idx.code}; if ({k} < 0) {k} += {n};")
         self.emit(f"if ({k} < 0 || {k} >= {n}) KS_RETURN(KS_RET_EXCEPTION);  // IndexError")
         if base.ty == GPUS:
-            return Val(GPU, f"(int){k}")
+            # "& 7" is the identity on a checked index; it keeps the shared-memory load in range when the compiler
+            # hoists it (ks_ns is a plain, non-volatile ld.shared) above the IndexError test
+            return Val(GPU, f"((int){k} & 7)")
         if base.ty == GPULIST:
-            return self.tmp(GPU, f"(int){base.code}.g[{k}]")
+            return self.tmp(GPU, f"((int){base.code}.g[{k}] & 7)")
         return self.tmp(INT if base.ty == ILIST else FLOAT, f"{base.code}.v[{k}]")
 
     # ------------------------------------------------------------------ expressions
@@ -1700,8 +1730,8 @@ def compile_policy(source: str) -> CompiledPolicy:
         if name in flagged:
             out.append(f"  int b_{name} = 0;")
     out.extend(tr.lines)
-    if falls:
-        out.append("  KS_RETURN(KS_RET_EXCEPTION);  // fell off the end: int(max(0, None)) raises TypeError")
+    # reached only by falling off the end of the Python function: int(max(0, None)) raises TypeError
+    out.append("  KS_RETURN(KS_RET_EXCEPTION);")
     out.append("}")
     cp = CompiledPolicy(source, "\n".join(out) + "\n", symbol, None, dict(tr.var_types), 1 if skip else 0)
     _CACHE[digest] = cp

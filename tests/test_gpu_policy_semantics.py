@@ -66,3 +66,43 @@ def test_shipped_policies_match_cpython_case_by_case(built_lib):
         want = np.array(cpython_scores(pol[n], objs), dtype=np.int64)
         bad = np.nonzero(got != want)[0]
         assert bad.size == 0, f"{n}: case {int(bad[0])}: device {int(got[bad[0]])} vs CPython {int(want[bad[0]])}"
+
+
+TRICKY = [
+    # IndexError far outside the node's GPUs: the bounds test must not be overtaken by a hoisted shared-memory load
+    "def priority_function(pod, node):\n    score = 1\n    for i in range(1, 4):\n        score = score + i * (node.gpus[pod.num_gpu].gpu_milli_left * 100.0)\n    return score\n",
+    "def priority_function(pod, node):\n    return node.gpus[pod.cpu_milli].gpu_milli_left + 1\n",
+    # a raise that only happens when short-circuit evaluation gets there: code after it stays reachable
+    "def priority_function(pod, node):\n    x = node.gpu_left and (1 / 0)\n    return 7 + x\n",
+    "def priority_function(pod, node):\n    x = 0 < node.gpu_left < (1 // 0)\n    return 3 + x\n",
+    "def priority_function(pod, node):\n    s = sum(1 / 0 for g in node.gpus)\n    return 5 + s\n",
+    "def priority_function(pod, node):\n    t = sorted(node.gpus, key=lambda g: undefined_name)\n    return 9 + len(t)\n",
+    "def priority_function(pod, node):\n    for g in node.gpus:\n        return nothing\n    return 11\n",
+    # Python number semantics
+    "def priority_function(pod, node):\n    return (-7 // 2) * -100 + (-7 % 3) * 10 + int(-7.5 % 2 * 2) + (7 // -2) * -1000\n",
+    "def priority_function(pod, node):\n    return max(1, 1.0) + min(2.0, 2) + round(2.5) + round(3.5) + int(-0.9) + abs(-3) + (True + True)\n",
+    "def priority_function(pod, node):\n    return sum([0.1, 0.2, 0.3, 0.1, 0.1, 0.1, 0.1, 0.1, 0.1, 0.1]) * 1e17 + sum(g.gpu_milli_left / 7 for g in node.gpus) * 1e13\n",
+    "def priority_function(pod, node):\n    return (node.cpu_milli_total ** 0.5) * 1e6 + 2 ** 10 + 2 ** -1 + (-8) ** 2\n",
+]
+
+
+def test_tricky_sources_match_cpython(built_lib):
+    from funsearch_kubernetes_simulator_b200 import ClusterSpec, Trace
+    from funsearch_kubernetes_simulator_b200.evaluator import BatchEvaluator
+    from funsearch_kubernetes_simulator_b200.policy_compiler import PolicyCompileError, compile_policy
+    srcs = []
+    for s in TRICKY:
+        try:
+            compile_policy(s)
+            srcs.append(s)
+        except PolicyCompileError:
+            pass
+    assert len(srcs) == len(TRICKY)
+    pods, ns, nc, objs = random_cases(256, seed=3)
+    ev = BatchEvaluator(ClusterSpec.load("gpu16"), [Trace.load("default").head(10)])
+    compiled = ev.compile(srcs, processes=0)
+    for slot, src in enumerate(srcs):
+        got = ev.debug_scores(compiled, slot, pods, ns, nc)
+        want = np.array(cpython_scores(src, objs), dtype=np.int64)
+        bad = np.nonzero(got != want)[0]
+        assert bad.size == 0, f"{src}\ncase {int(bad[0])}: device {int(got[bad[0]])} vs CPython {int(want[bad[0]])}"
