@@ -173,15 +173,19 @@ KS_D double ks_ipow_neg(ks_int a, ks_int b, int* st) { return ks_fpow(ks_i2d(a),
 
 // int(x) for float x: truncation; OverflowError on inf, ValueError on nan.
 KS_D ks_int ks_f2i(double x, int* st) {
-  if (isnan(x) || isinf(x)) { ks_fail(st, 1); return 0; }
-  if (x >= 9223372036854775808.0 || x <= -9223372036854775808.0) { ks_fail(st, 2); return 0; }
+  if (!(fabs(x) < 9223372036854775808.0)) {  // nan, inf, or beyond int64 (one test on the common path)
+    ks_fail(st, (isnan(x) || isinf(x)) ? 1 : 2);
+    return 0;
+  }
   return (ks_int)x;  // cvt.rzi
 }
 // round(x) with one argument: half to even, result is an int.
 KS_D ks_int ks_fround(double x, int* st) {
-  if (isnan(x) || isinf(x)) { ks_fail(st, 1); return 0; }
-  double r = rint(x);
-  if (r >= 9223372036854775808.0 || r <= -9223372036854775808.0) { ks_fail(st, 2); return 0; }
+  const double r = rint(x);
+  if (!(fabs(r) < 9223372036854775808.0)) {
+    ks_fail(st, (isnan(x) || isinf(x)) ? 1 : 2);
+    return 0;
+  }
   return (ks_int)r;
 }
 KS_D double ks_msqrt(double x, int* st) {
@@ -350,8 +354,7 @@ KS_D int ks_slice_bound(ks_int b, int n) {
 KS_D long long ks_wrap_i(ks_int s) { return s > 0 ? s : 0; }
 KS_D long long ks_wrap_f(double s) {
   if (!(s > 0.0)) return 0;  // max(0, nan) -> 0, max(0, -x) -> 0, max(0, 0.0) -> 0
-  if (isinf(s)) return KS_RET_EXCEPTION;  // int(inf): OverflowError
-  if (s >= 9223372036854775808.0) return KS_RET_UNSUPPORTED;
+  if (!(s < 9223372036854775808.0)) return isinf(s) ? KS_RET_EXCEPTION : KS_RET_UNSUPPORTED;  // int(inf): OverflowError
   return (long long)s;
 }
 KS_D long long ks_wrap_n(KsNum s) { return s.f ? ks_wrap_f(s.d) : ks_wrap_i(s.i); }

@@ -83,6 +83,9 @@ TRICKY = [
     "def priority_function(pod, node):\n    return max(1, 1.0) + min(2.0, 2) + round(2.5) + round(3.5) + int(-0.9) + abs(-3) + (True + True)\n",
     "def priority_function(pod, node):\n    return sum([0.1, 0.2, 0.3, 0.1, 0.1, 0.1, 0.1, 0.1, 0.1, 0.1]) * 1e17 + sum(g.gpu_milli_left / 7 for g in node.gpus) * 1e13\n",
     "def priority_function(pod, node):\n    return (node.cpu_milli_total ** 0.5) * 1e6 + 2 ** 10 + 2 ** -1 + (-8) ** 2\n",
+    # int() of a three-way mixed max: an earlier shape of ks_f2i was mis-optimised by NVVM here (always 'raised')
+    "def priority_function(pod, node):\n    t = -0.25 / 1e6\n    return int(max(t, 1e6, node.memory_mib_left))\n",
+    "def priority_function(pod, node):\n    return int(min(node.cpu_milli_left * 0.5, 1e30, pod.cpu_milli)) + round(max(0.5, node.gpu_left, 2.5))\n",
 ]
 
 

@@ -32,5 +32,8 @@ for slot, (seed, src) in enumerate(srcs):
         i = int(d[0]); pod, node = objs[i]
         print(f"MISMATCH seed {seed} case {i}: device {int(got[i])} cpython {int(want[i])} ({d.size} cases)"); print(src)
         print("pod", vars(pod)); print("node", node.cpu_milli_left, node.memory_mib_left, node.gpu_left, node.cpu_milli_total, node.memory_mib_total, [g.gpu_milli_left for g in node.gpus])
+        for j in d[:12]:
+            pj, nj = objs[int(j)]
+            print("   case", int(j), "dev", int(got[j]), "py", int(want[j]), "pod", pj.cpu_milli, pj.memory_mib, pj.num_gpu, pj.gpu_milli, "node", nj.cpu_milli_left, nj.memory_mib_left, nj.gpu_left, [g.gpu_milli_left for g in nj.gpus])
         if bad >= 3: break
 print("done", len(srcs), "policies,", bad, "mismatching")
