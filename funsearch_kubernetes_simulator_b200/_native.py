@@ -93,6 +93,7 @@ _SIGNATURES = {
     "ks_eval_batch_host": (C.c_int, [C.c_longlong, C.POINTER(KsPlan), C.POINTER(KsHostBatch), C.c_void_p, C.c_longlong,
                                      C.c_void_p, C.POINTER(C.c_longlong), C.POINTER(C.c_longlong)]),
     "ks_debug_pow": (C.c_int, [C.c_longlong, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]),
+    "ks_debug_math": (C.c_int, [C.c_longlong, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]),
     "ks_debug_score": (C.c_int, [C.c_longlong, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "ks_launch_count": (C.c_longlong, []),
     "ks_shutdown": (C.c_int, []),

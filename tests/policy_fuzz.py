@@ -96,8 +96,12 @@ class Gen:
             return f"({a} if {self.cond(d + 1)} else {self.expr(d + 1)})"
         if k < 0.88:
             return f"({a} {r.choice(['and', 'or'])} {self.expr(d + 1)})"
-        if k < 0.93:
+        if k < 0.91:
             return f"math.sqrt(abs({a}))"
+        if k < 0.94:
+            return f"math.log({r.choice(['1 + ', '0.5 + ', '1e-9 + '])}abs({a}))"
+        if k < 0.96:
+            return f"math.exp({r.choice(['-', ''])}abs({a}) / {r.choice(['1000.0', '100000', '7.0'])})"
         return f"({a} / max(1, {self.expr(d + 1)}))"
 
     def cond(self, d=0):

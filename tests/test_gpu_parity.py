@@ -320,3 +320,47 @@ def test_device_pow_is_bit_identical_to_host_libm(env):
     want = np.array([math.pow(a, b) for a, b in zip(x.tolist(), y.tolist())])
     bad = np.nonzero(got.view(np.uint64) != want.view(np.uint64))[0]
     assert bad.size == 0, f"{bad.size} of {n} differ, e.g. x={x[bad[0]]!r} y={y[bad[0]]!r} got={got[bad[0]]!r} want={want[bad[0]]!r}"
+
+
+def test_device_exp_log_bit_identical_to_host_libm(env):
+    """math.exp / math.log in a policy are glibc's exp and log; the device versions (csrc/ks_glibc_explog.h) must return
+    the same bits as this host's libm over the whole domain, overflow, subnormal results and subnormal arguments included."""
+    import ctypes as C
+    import math
+    import numpy as np
+    import torch
+    from funsearch_kubernetes_simulator_b200 import _native as nat
+    ev = env["BatchEvaluator"](env["ClusterSpec"].load("gpu16"), [env["Trace"].load("default").head(10)])
+    compiled = ev.compile([env["pol"]["ts_first_fit"]])
+    prog = ev._program((compiled[0].handle,))
+    rng = np.random.default_rng(13)
+    n = 200000
+    q = n // 5
+
+    def run(op, x):
+        dx = torch.from_numpy(x).cuda()
+        out = torch.empty_like(dx)
+        nat.check(nat.lib().ks_debug_math(prog, op, C.c_void_p(dx.data_ptr()), C.c_void_p(dx.data_ptr()), C.c_void_p(out.data_ptr()),
+                                          len(x), C.c_void_p(torch.cuda.current_stream().cuda_stream)))
+        return out.cpu().numpy()
+
+    def host(fn, x):
+        out = np.empty_like(x)
+        for i, v in enumerate(x.tolist()):
+            try:
+                out[i] = fn(v)
+            except OverflowError:
+                out[i] = math.inf
+        return out
+
+    xe = np.concatenate([(rng.random(q) - 0.5) * 4, (rng.random(q) - 0.5) * 1500, -700 - rng.random(q) * 50,
+                         (rng.random(q) - 0.5) * 1e-10, 700 + rng.random(q) * 12, np.array([0.0, -0.0, math.inf, -math.inf, 709.782712893384, -745.2])])
+    got, want = run(1, xe), host(math.exp, xe)
+    bad = np.nonzero(got.view(np.uint64) != want.view(np.uint64))[0]
+    assert bad.size == 0, f"exp: {bad.size} differ, e.g. x={xe[bad[0]]!r} got={got[bad[0]]!r} want={want[bad[0]]!r}"
+    xl = np.concatenate([0.9 + rng.random(q) * 0.2, np.exp((rng.random(q) - 0.5) * 1400), rng.integers(1, 2000000, q).astype(np.float64),
+                         rng.integers(1, 2 ** 52, q).astype(np.uint64).view(np.float64),
+                         rng.random(q) * 1000 + 1e-300, np.array([1.0, math.inf, 5e-324, 2.2250738585072014e-308])])
+    got, want = run(2, xl), host(math.log, xl)
+    bad = np.nonzero(got.view(np.uint64) != want.view(np.uint64))[0]
+    assert bad.size == 0, f"log: {bad.size} differ, e.g. x={xl[bad[0]]!r} got={got[bad[0]]!r} want={want[bad[0]]!r}"

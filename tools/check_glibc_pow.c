@@ -18,6 +18,7 @@ static inline double dbl_of(uint64_t u) { double d; memcpy(&d, &u, 8); return d;
 #define KS_PF_FN static inline
 #include "../funsearch_kubernetes_simulator_b200/csrc/ks_glibc_pow_tables.inc"
 #include "../funsearch_kubernetes_simulator_b200/csrc/ks_glibc_pow.h"
+#include "../funsearch_kubernetes_simulator_b200/csrc/ks_glibc_explog.h"
 
 static uint64_t rng = 88172645463325252ull;
 static uint64_t next(void) { rng ^= rng << 13; rng ^= rng >> 7; rng ^= rng << 17; return rng; }
@@ -44,6 +45,41 @@ int main(int argc, char** argv) {
       bad++;
     }
   }
-  printf("checked %ld pairs, %ld on the fast path, %ld mismatches\n", n, fast, bad);
-  return bad != 0;
+  printf("pow: checked %ld pairs, %ld on the fast path, %ld mismatches\n", n, fast, bad);
+  /* exp and log: the whole domain, no fallback */
+  long ebad = 0, lbad = 0;
+  for (long it = 0; it < n; ++it) {
+    double x;
+    switch (it & 7) {
+      case 0: x = (uni() - 0.5) * 4.0; break;
+      case 1: x = (uni() - 0.5) * 1500.0; break;                 /* through overflow and the subnormal results */
+      case 2: x = -700.0 - uni() * 50.0; break;                  /* subnormal results */
+      case 3: x = dbl_of(next()); break;                         /* any bit pattern */
+      case 4: x = (uni() - 0.5) * 1e-10; break;
+      case 5: x = 700.0 + uni() * 12.0; break;
+      default: x = (uni() - 0.5) * 60.0; break;
+    }
+    double got = ks_glibc_exp(x), want = exp(x);
+    if (bits_of(got) != bits_of(want) && !(got != got && want != want)) {
+      if (ebad < 10) printf("EXP MISMATCH x=%a got=%a want=%a\n", x, got, want);
+      ebad++;
+    }
+    switch (it & 7) {
+      case 0: x = 0.9 + uni() * 0.2; break;                      /* the near-1 polynomial and its borders */
+      case 1: x = exp((uni() - 0.5) * 1400.0); break;
+      case 2: x = dbl_of(next() & 0x7fffffffffffffffull); break; /* any non-negative bit pattern, subnormals included */
+      case 3: x = (double)(next() % 2000000 + 1); break;
+      case 4: x = dbl_of(next() % 0x10000000000000ull); break;   /* subnormals */
+      case 5: x = 1.0 + (uni() - 0.5) * 1e-8; break;
+      default: x = uni() * 1000.0; break;
+    }
+    if (x != x || x == 0.0) continue;
+    got = ks_glibc_log(x), want = log(x);
+    if (bits_of(got) != bits_of(want)) {
+      if (lbad < 10) printf("LOG MISMATCH x=%a got=%a want=%a\n", x, got, want);
+      lbad++;
+    }
+  }
+  printf("exp: %ld operands, %ld mismatches; log: %ld mismatches\n", n, ebad, lbad);
+  return bad != 0 || ebad != 0 || lbad != 0;
 }
