@@ -18,8 +18,8 @@ ST_OK, ST_POLICY_EXCEPTION, ST_GPU_SHORTFALL, ST_STEP_BUDGET, ST_UNSUPPORTED, ST
 STATUS_NAMES = {0: "ok", 1: "policy_exception", 2: "gpu_shortfall", 3: "step_budget", 4: "unsupported", 5: "capacity"}
 
 KS_POD_INTS = 8
-KS_NC_FIELDS = 19
-KS_NS_FIELDS = 11
+KS_NC_FIELDS = 20
+KS_NS_FIELDS = 12
 KS_NODE_NONE = 0xFFFF
 KS_NODE_WAITING = 0xFFFE
 KS_MAX_TIME = (1 << 39) - 2

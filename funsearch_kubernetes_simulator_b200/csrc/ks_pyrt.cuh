@@ -43,12 +43,12 @@ extern "C" __device__ ks_int ks_rt_idiv(ks_int a, ks_int b);  // C truncating qu
 // ------------------------------------------------------------------------------- field access
 // mutable node state: a plain shared-memory load (not volatile: the state does not change while a policy
 // is being evaluated, so the compiler may merge repeated reads of one field)
-KS_D int ks_ns(unsigned ns, int nss, int field) {
+KS_D int ks_ns(unsigned ns, int field) {
   int v;
-  asm("ld.shared.s32 %0, [%1];" : "=r"(v) : "r"(ns + (unsigned)(field * nss)));
+  asm("ld.shared.s32 %0, [%1];" : "=r"(v) : "r"(ns + 4u * (unsigned)field));
   return v;
 }
-KS_D int ks_nc(const int* nc, int stride, int field) { return __ldg(nc + field * stride); }
+KS_D int ks_nc(const int* nc, int field) { return __ldg(nc + field); }
 // fp64 division, shared by every policy of the module (keeps the per-policy code small)
 extern "C" __device__ double ks_rt_ddiv(double a, double b);
 #ifdef KS_INLINE_DIV

@@ -270,8 +270,8 @@ class BatchEvaluator:
 
     # ------------------------------------------------------------------ test hook: raw scores of (pod, node) cases
     def debug_scores(self, policies: Sequence[CompiledPolicy], slot: int, pods: np.ndarray, ns: np.ndarray, nc: np.ndarray) -> np.ndarray:
-        """Wrapped scores of policies[slot] for independent cases: pods [n, 6] int64, ns [KS_NS_FIELDS, n] int32,
-        nc [KS_NC_FIELDS, n] int32 (ks_debug_score).  -1 = the policy raised, -2 = left the supported subset."""
+        """Wrapped scores of policies[slot] for independent cases: pods [n, 6] int64, ns [n, KS_NS_FIELDS] int32,
+        nc [n, KS_NC_FIELDS] int32 (ks_debug_score; field numbering of include/ks_abi.h).  -1 = the policy raised, -2 = left the supported subset."""
         torch = self._torch
         n = pods.shape[0]
         prog = self._program(tuple(int(p.handle) for p in policies))

@@ -309,8 +309,8 @@ class _Translator:
             raise _Returned()
         arr, f = GPU_FIELDS[attr]
         if arr == "ns":
-            return self.tmp(INT, f"(ks_int)ks_ns(ns, nss, {f} + {g.code})", bits=25)
-        return self.tmp(INT, f"(ks_int)ks_nc(nc, ncs, {f} + {g.code})", bits=31)
+            return self.tmp(INT, f"(ks_int)ks_ns(ns, {f} + {g.code})", bits=25)
+        return self.tmp(INT, f"(ks_int)ks_nc(nc, {f} + {g.code})", bits=31)
 
     def attribute(self, node: ast.Attribute) -> Val:
         base = self.expr(node.value)
@@ -325,9 +325,9 @@ class _Translator:
             raise _Returned()
         if base.ty == NODE:
             if a in NODE_STATE:
-                return self.tmp(INT, f"(ks_int)ks_ns(ns, nss, {NODE_STATE[a]})", bits=32)
+                return self.tmp(INT, f"(ks_int)ks_ns(ns, {NODE_STATE[a]})", bits=32)
             if a in NODE_CONST:
-                return self.tmp(INT, f"(ks_int)ks_nc(nc, ncs, {NODE_CONST[a]})", bits=31)
+                return self.tmp(INT, f"(ks_int)ks_nc(nc, {NODE_CONST[a]})", bits=31)
             if a == "gpus":
                 return Val(GPUS)
             if a == "node_id":
@@ -1717,7 +1717,7 @@ def compile_policy(source: str) -> CompiledPolicy:
     out = [f"// translated from a priority_function(pod, node) source, sha256 {digest[:16]}",
            f'extern "C" __device__ long long {symbol}(KS_POLICY_PARAMS) {{',
            "  int st = 0; (void)st;",
-           "  const int ngpus = ks_nc(nc, ncs, KS_NC_NUM_GPUS); (void)ngpus;"]
+           "  const int ngpus = ks_nc(nc, KS_NC_NUM_GPUS); (void)ngpus;"]
     if tr.uses_budget:
         out.append(f"  int budget = {LOOP_BUDGET};")
     for name in sorted(tr.var_types):

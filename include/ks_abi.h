@@ -37,20 +37,22 @@
 #define KS_MAX_NODES 0xFFF0
 #define KS_MAX_GPUS_PER_NODE 8
 
-// ---- mutable per-node state, structure-of-arrays with stride n_pad (ints) ---------------
+// ---- mutable per-node state: KS_NS_FIELDS ints per node, node-major (48 bytes, 16-byte aligned rows) -----
+// Rows are contiguous so that the kernel reads a node with three 16-byte loads and a policy addresses a field
+// as base + constant.  Slot 3 is padding; GPU slots a node does not have hold 0 for the whole episode.
 #define KS_NS_CPU_LEFT 0
 #define KS_NS_MEM_LEFT 1
 #define KS_NS_GPU_LEFT 2
-#define KS_NS_GPU_MILLI_LEFT 3  // .. +7
-#define KS_NS_FIELDS 11
+#define KS_NS_GPU_MILLI_LEFT 4  // .. +7
+#define KS_NS_FIELDS 12
 
-// ---- constant per-node data, structure-of-arrays with stride n_pad (ints) ---------------
+// ---- constant per-node data: KS_NC_FIELDS ints per node, node-major (80 bytes) ----------------------------
 #define KS_NC_CPU_TOTAL 0
 #define KS_NC_MEM_TOTAL 1
 #define KS_NC_NUM_GPUS 2
-#define KS_NC_GPU_MILLI_TOTAL 3  // .. +7
-#define KS_NC_GPU_MEM_TOTAL 11   // .. +7   (GPU.memory_mib_total == memory_mib_left: never mutated)
-#define KS_NC_FIELDS 19
+#define KS_NC_GPU_MILLI_TOTAL 4  // .. +7
+#define KS_NC_GPU_MEM_TOTAL 12   // .. +7   (GPU.memory_mib_total == memory_mib_left: never mutated)
+#define KS_NC_FIELDS 20
 
 // ---- packed pod record, indexed by id_rank, 32 bytes -------------------------------------
 #define KS_POD_CPU 0
@@ -66,12 +68,11 @@
 // ---- policy function ABI ---------------------------------------------------------------
 // One translated priority_function(pod, node).  The pod's fields (entities.py:30-43) travel in registers
 // (p_ctime is the retry-mutated creation_time == time of the creation event being handled); `ns` is the
-// SHARED-memory byte address of this node's first mutable field (field f at ns + f * nss), `nc` points
-// at this node's first constant field in global memory (field f at nc[f * ncs]).
+// SHARED-memory byte address of this node's state row (field f at ns + 4 * f), `nc` points at this node's
+// row of constants in global memory (field f at nc[f]).
 // Returns int(max(0, score)) >= 0, or KS_RET_EXCEPTION / KS_RET_UNSUPPORTED.
-#define KS_POLICY_PARAMS                                                                              \
-  int p_cpu, int p_mem, int p_ngpu, int p_gmilli, long long p_ctime, long long p_dur, unsigned ns, int nss, \
-      const int *__restrict__ nc, int ncs
+#define KS_POLICY_PARAMS \
+  int p_cpu, int p_mem, int p_ngpu, int p_gmilli, long long p_ctime, long long p_dur, unsigned ns, const int *__restrict__ nc
 typedef long long (*ks_policy_fn)(KS_POLICY_PARAMS);
 // flags of a dispatch-table entry
 #define KS_PF_PREFIX_HOISTED 1  // the source began with the reference template's feasibility prefix
@@ -117,23 +118,23 @@ struct KsLaunch {
   const KsTraceDev* traces;
   const int* ep_policy;  // [n_episodes] slot in the linked policy table
   const int* ep_trace;   // [n_episodes]
-  const int* nconst;     // [KS_NC_FIELDS * n_pad]
+  const int* nconst;     // [n_pad][KS_NC_FIELDS]
   int* work_counter;     // zeroed by the host before launch; episodes are pulled in table order
   KsResult* results;     // [n_episodes]
   unsigned long long* placements;  // optional; episode e writes [place_off[e], +n_pods)
   const long long* place_off;      // [n_episodes] or null
-  unsigned char* scratch;          // per resident team: heap tail + (placements if not requested) + waiting tail
+  unsigned char* scratch;          // per resident team: event heap + (placements if not requested) + waiting list
   long long scratch_per_team;
   long long scratch_place_off;  // byte offset of the placement records inside a team's scratch (if not an output)
-  long long scratch_wait_off;   // byte offset of the waiting-list overflow inside a team's scratch
+  long long scratch_wait_off;   // byte offset of the waiting list inside a team's scratch
   long long tot_cpu, tot_mem, tot_gpu_count, tot_gpu_milli;
   long long max_events;  // 0 = unlimited
   double snapshot_interval;
   int n_episodes;
   int n_nodes;
   int n_pad;
-  int heap_smem_entries;  // heap[0, S) lives in shared memory, the rest in scratch
-  int wait_smem_entries;  // waiting list [0, W) in shared memory, the rest in scratch
+  int heap_smem_entries;  // reserved (0): the heap lives in the team's scratch, L1-resident
+  int wait_smem_entries;  // reserved (0)
   int max_pods;           // largest n_pods over the traces of this batch (sizes the scratch regions)
   int smem_per_team;      // bytes
   int warps_per_team;     // warps cooperating on one episode (1 = warp per episode)

@@ -20,7 +20,7 @@
 extern "C" {
 #endif
 
-#define KS_API_VERSION 1
+#define KS_API_VERSION 2
 
 /* Error text of the last failing call on this thread.  Replaces the Python exception text the
  * reference's worker swallows (funsearch/funsearch_integration.py:63-64). */
@@ -91,7 +91,7 @@ int ks_program_link_check(int n_policies, const long long* policies, long long* 
 /* ---- evaluation ----------------------------------------------------------------------------- */
 
 /* Launch geometry and scratch requirement for a batch.  Fill n_episodes, n_nodes, max_pods,
- * want_placements and (optionally, 0 = choose) warps_per_team / teams_per_block / heap_smem_entries; the call fills the
+ * want_placements and (optionally, 0 = choose) warps_per_team / teams_per_block / ctas_per_sm; the call fills the
  * rest.  Purely arithmetic apart from reading the device's SM count and shared-memory limit. */
 typedef struct KsPlan {
   int n_episodes;
@@ -100,8 +100,8 @@ typedef struct KsPlan {
   int want_placements;
   int warps_per_team;    /* warps replaying one episode together (0 = choose: 1 up to 64 nodes, else one lane per node) */
   int teams_per_block;   /* episodes in flight per CTA */
-  int heap_smem_entries; /* event-heap entries kept in shared memory per team */
-  int wait_smem_entries;
+  int heap_smem_entries; /* reserved, returned as 0: the event heap lives in the team's scratch (L1/L2-resident) */
+  int wait_smem_entries; /* reserved, returned as 0 */
   int ctas_per_sm;       /* 0 = choose; 2 = throughput variant of the kernel (128 registers, two CTAs per SM) */
   int blocks;
   int smem_per_team;
@@ -204,8 +204,8 @@ int ks_debug_math(long long program, int op, const double* x, const double* y, d
 /* Test hook: the wrapped score int(max(0, priority_function(pod, node))) of policy-table slot `slot` for n independent
  * (pod, node) cases, obtained exactly as the replay kernel obtains it; KS_RET_EXCEPTION / KS_RET_UNSUPPORTED where the policy
  * raises / leaves the subset.  Replaces a direct call of FunSearchScheduler.__call__ (funsearch_integration.py:91-101).
- * Device pointers: pods [n][6] int64 (cpu, mem, num_gpu, gpu_milli, creation_time, duration), ns [KS_NS_FIELDS][n],
- * nc [KS_NC_FIELDS][n], out [n]. */
+ * Device pointers: pods [n][6] int64 (cpu, mem, num_gpu, gpu_milli, creation_time, duration), ns [n][KS_NS_FIELDS],
+ * nc [n][KS_NC_FIELDS] (rows as in ks_abi.h), out [n]. */
 int ks_debug_score(long long program, int slot, int n, const long long* pods, const int* ns, const int* nc, long long* out,
                    void* stream);
 

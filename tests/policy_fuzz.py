@@ -177,8 +177,8 @@ def random_cases(n, seed):
     """n independent (pod, node) cases: arrays for the device hook plus entity-shaped objects for CPython."""
     rng = np.random.default_rng(seed)
     pods = np.zeros((n, 6), dtype=np.int64)
-    ns = np.zeros((11, n), dtype=np.int32)
-    nc = np.zeros((19, n), dtype=np.int32)
+    ns = np.zeros((n, 12), dtype=np.int32)   # rows of KS_NS_FIELDS (include/ks_abi.h)
+    nc = np.zeros((n, 20), dtype=np.int32)   # rows of KS_NC_FIELDS
     objs = []
     for i in range(n):
         ngpus = int(rng.choice([0, 1, 2, 4, 8, 3]))
@@ -196,12 +196,12 @@ def random_cases(n, seed):
         p_gm = int(rng.choice([0, 1000, int(rng.integers(1, 1001))])) if p_ng else 0
         ct, du = int(rng.integers(0, 10 ** 7)), int(rng.integers(0, 10 ** 6))
         pods[i] = (p_cpu, p_mem, p_ng, p_gm, ct, du)
-        ns[0, i], ns[1, i], ns[2, i] = cpu_l, mem_l, gl
-        nc[0, i], nc[1, i], nc[2, i] = cpu_t, mem_t, ngpus
+        ns[i, 0], ns[i, 1], ns[i, 2] = cpu_l, mem_l, gl
+        nc[i, 0], nc[i, 1], nc[i, 2] = cpu_t, mem_t, ngpus
         for g in range(ngpus):
-            ns[3 + g, i] = gml[g]
-            nc[3 + g, i] = gmt[g]
-            nc[11 + g, i] = gmem[g]
+            ns[i, 4 + g] = gml[g]
+            nc[i, 4 + g] = gmt[g]
+            nc[i, 12 + g] = gmem[g]
         pod = NS(pod_id=f"p{i}", cpu_milli=p_cpu, memory_mib=p_mem, num_gpu=p_ng, gpu_milli=p_gm, gpu_spec="", creation_time=ct,
                  duration_time=du, assigned_node="", assigned_gpus=[])
         node = NS(node_id=f"n{i}", cpu_milli_left=cpu_l, cpu_milli_total=cpu_t, memory_mib_left=mem_l, memory_mib_total=mem_t,

@@ -74,18 +74,19 @@ def test_edge_cases(env):
         _run_group(env, cluster, {"e": trace}, [(tag, "e", edge["policy"])])
 
 
-def test_heap_in_global_memory_gives_identical_results(env):
-    """The shared/global split of the event heap must not be observable."""
+def test_launch_geometry_is_not_observable(env):
+    """Episodes per CTA, and whether the placement records are an output or live in the team's scratch, must not
+    change any result."""
     cluster = env["ClusterSpec"].load("gpu16")
     tr = env["Trace"].load("default")
     ev = env["BatchEvaluator"](cluster, [tr])
     pn = ["ts_funsearch_4901", "ts_first_fit"]
     compiled = ev.compile([env["pol"][p] for p in pn])
-    for S in (512, 1024, 8152):
-        outs = ev.run_episodes(compiled, [0, 1], [0, 0], want_placements=True, heap_smem_entries=S)
-        assert ev.last_plan.heap_smem_entries == S
+    for teams in (1, 2, 8):
+        outs = ev.run_episodes(compiled, [0, 1], [0, 0], want_placements=True, teams_per_block=teams)
+        assert ev.last_plan.teams_per_block == teams and ev.last_plan.heap_smem_entries == 0
         for p, out in zip(pn, outs):
-            assert_matches_golden(f"S={S} {p}", env["gold"]["runs"][f"default|gpu16|{p}"], out, tr, cluster)
+            assert_matches_golden(f"teams={teams} {p}", env["gold"]["runs"][f"default|gpu16|{p}"], out, tr, cluster)
     outs = ev.run_episodes(compiled, [0, 1], [0, 0], want_placements=False)
     for p, out in zip(pn, outs):
         assert_matches_golden(f"no placements {p}", env["gold"]["runs"][f"default|gpu16|{p}"], out, tr, cluster)

@@ -94,7 +94,7 @@ def test_library_exports_every_declared_symbol(built_lib):
         assert hasattr(lib, name), f"{name} declared in include/ks_b200.h but not exported"
     from funsearch_kubernetes_simulator_b200 import _native as nat
     assert declared == set(nat.EXPORTED_SYMBOLS)
-    assert nat.lib().ks_api_version() == 1
+    assert nat.lib().ks_api_version() == 2
 
 
 def test_no_gpu_means_loud_failure(built_lib):
@@ -145,14 +145,15 @@ def test_trace_pack_rejects_bad_input(built_lib):
 
 
 def test_cluster_pack(built_lib):
-    from funsearch_kubernetes_simulator_b200 import ClusterSpec
+    from funsearch_kubernetes_simulator_b200 import ClusterSpec, _native as nat
     c = ClusterSpec.load("gpu16")
     nconst, totals = c.packed()
     assert totals.tolist() == [1184000, 5898240, 64, 64000]
-    n_pad = 32
-    assert nconst[0 * n_pad: 0 * n_pad + 16].tolist() == c.cpu_total.tolist()
-    assert nconst[2 * n_pad: 2 * n_pad + 16].tolist() == c.num_gpus.tolist()
-    assert nconst[2 * n_pad + 16: 3 * n_pad].tolist() == [0] * 16
+    rows = nconst.reshape(32, nat.KS_NC_FIELDS)   # node-major rows, padded to 32 nodes
+    assert rows[:16, 0].tolist() == c.cpu_total.tolist()
+    assert rows[:16, 2].tolist() == c.num_gpus.tolist()
+    assert rows[:16, 4:12].tolist() == c.gpu_milli_total.tolist() and rows[:16, 12:20].tolist() == c.gpu_mem_total.tolist()
+    assert not rows[16:].any() and not rows[:, 3].any()
     big = ClusterSpec.load("all1523").head(1024)
     assert big.n_pad == 1024 and big.packed()[1][2] == int(big.num_gpus.sum())
 
@@ -163,11 +164,11 @@ def test_plan_arithmetic(built_lib):
     p.n_episodes, p.n_nodes, p.max_pods, p.want_placements = 1024, 16, 8152, 0
     nat.check(nat.lib().ks_plan(C.byref(p)))
     assert p.warps_per_team == 1 and 1 <= p.teams_per_block <= 8 and (p.blocks * p.teams_per_block >= 1024 or p.blocks == 148)
-    assert p.smem_per_block <= 232448 and p.heap_smem_entries % 2 == 0
+    assert p.smem_per_block <= 232448 and p.heap_smem_entries == 0
     assert p.scratch_bytes >= 256 + p.blocks * p.teams_per_block * p.scratch_per_team
     q = nat.KsPlan()
     q.n_episodes, q.n_nodes, q.max_pods, q.want_placements = 3, 1024, 100, 1
     nat.check(nat.lib().ks_plan(C.byref(q)))
-    assert q.blocks == 3 and q.teams_per_block == 1 and q.heap_smem_entries == 100 and q.warps_per_team == 16
+    assert q.blocks == 3 and q.teams_per_block == 1 and q.warps_per_team == 16 and q.smem_per_team >= 1024 * 48
     bad = nat.KsPlan()
     assert nat.lib().ks_plan(C.byref(bad)) != 0
