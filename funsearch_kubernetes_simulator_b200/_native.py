@@ -22,6 +22,7 @@ KS_NC_FIELDS = 20
 KS_NS_FIELDS = 12
 KS_NODE_NONE = 0xFFFF
 KS_NODE_WAITING = 0xFFFE
+KS_SCRATCH_HEADER = 4096
 KS_MAX_TIME = (1 << 39) - 2
 KS_STATIC_SCRATCH_BYTES = 32 << 20
 KS_PF_PREFIX_HOISTED = 1

@@ -36,6 +36,7 @@
 #define KS_NODE_WAITING 0xFFFEu  // failed at least once and not placed (member of waiting_pods)
 #define KS_MAX_NODES 0xFFF0
 #define KS_MAX_GPUS_PER_NODE 8
+#define KS_SCRATCH_HEADER 4096   // bytes in front of the per-team scratch: one work counter per CTA (<= 1024 CTAs)
 
 // ---- mutable per-node state: KS_NS_FIELDS ints per node, node-major (48 bytes, 16-byte aligned rows) -----
 // Rows are contiguous so that the kernel reads a node with three 16-byte loads and a policy addresses a field
@@ -119,7 +120,7 @@ struct KsLaunch {
   const int* ep_policy;  // [n_episodes] slot in the linked policy table
   const int* ep_trace;   // [n_episodes]
   const int* nconst;     // [n_pad][KS_NC_FIELDS]
-  int* work_counter;     // zeroed by the host before launch; episodes are pulled in table order
+  int* work_counter;     // [gridDim.x] zeroed by the host before launch: next entry of each CTA's range of the table
   KsResult* results;     // [n_episodes]
   unsigned long long* placements;  // optional; episode e writes [place_off[e], +n_pods)
   const long long* place_off;      // [n_episodes] or null

@@ -107,7 +107,7 @@ typedef struct KsPlan {
   int smem_per_team;
   int smem_per_block;
   long long scratch_per_team;
-  long long scratch_bytes; /* total device scratch the caller must provide (256-byte header included) */
+  long long scratch_bytes; /* total device scratch the caller must provide (KS_SCRATCH_HEADER bytes of work counters included) */
 } KsPlan;
 int ks_plan(KsPlan* plan);
 
@@ -146,13 +146,13 @@ int ks_eval_batch(long long program, const KsPlan* plan, const KsBatch* batch, v
  *
  * Limit: plan->scratch_bytes must not exceed KS_STATIC_SCRATCH_BYTES, otherwise the call fails with a
  * message stating both numbers.  A plan that is too large can be shrunk by lowering plan->blocks
- * (fewer resident teams; the kernel pulls episodes from a queue, so any block count is correct) and
- * setting plan->scratch_bytes = 256 + plan->scratch_per_team * plan->blocks * plan->teams_per_block.
+ * (fewer resident teams; the kernel hands out the episode table dynamically, so any block count is correct) and
+ * setting plan->scratch_bytes = KS_SCRATCH_HEADER + plan->scratch_per_team * plan->blocks * plan->teams_per_block.
  *
  * Set-up: the first call on each device looks up the array's device address (cudaGetSymbolAddress,
  * with that device current) and remembers it; make that first call before any stream capture begins.
  * Sharing: every call on a device uses the same array, which keeps the previous call's contents.  The
- * work counter at its start is cleared on `stream` before each launch and the kernel rewrites every
+ * work counters at its start are cleared on `stream` before each launch and the kernel rewrites every
  * other byte it reads, so back-to-back calls on one stream are fine, but two calls that can overlap
  * on the GPU (different streams, different threads) race on the array and must be serialised by the
  * caller. */

@@ -165,7 +165,7 @@ def test_plan_arithmetic(built_lib):
     nat.check(nat.lib().ks_plan(C.byref(p)))
     assert p.warps_per_team == 1 and 1 <= p.teams_per_block <= 8 and (p.blocks * p.teams_per_block >= 1024 or p.blocks == 148)
     assert p.smem_per_block <= 232448 and p.heap_smem_entries == 0
-    assert p.scratch_bytes >= 256 + p.blocks * p.teams_per_block * p.scratch_per_team
+    assert p.scratch_bytes >= nat.KS_SCRATCH_HEADER + p.blocks * p.teams_per_block * p.scratch_per_team
     q = nat.KsPlan()
     q.n_episodes, q.n_nodes, q.max_pods, q.want_placements = 3, 1024, 100, 1
     nat.check(nat.lib().ks_plan(C.byref(q)))

@@ -80,8 +80,8 @@ def test_static_scratch_limit_and_shrunk_plan(built_lib):
     want = rb.results().copy()
     small = nat.KsPlan()
     C.memmove(C.byref(small), C.byref(rb.plan), C.sizeof(nat.KsPlan))
-    small.blocks = max(1, int((nat.KS_STATIC_SCRATCH_BYTES - 256) // (small.scratch_per_team * small.teams_per_block)))
-    small.scratch_bytes = 256 + small.scratch_per_team * small.blocks * small.teams_per_block
+    small.blocks = max(1, int((nat.KS_STATIC_SCRATCH_BYTES - nat.KS_SCRATCH_HEADER) // (small.scratch_per_team * small.teams_per_block)))
+    small.scratch_bytes = nat.KS_SCRATCH_HEADER + small.scratch_per_team * small.blocks * small.teams_per_block
     assert small.blocks < rb.plan.blocks and small.scratch_bytes <= nat.KS_STATIC_SCRATCH_BYTES
     rb.d_res.zero_()
     rc = _static_call(ev, rb, small)
