@@ -69,6 +69,16 @@ class EpisodeOutcome:
         return placed[key]
 
 
+def table_order(ep_policy: np.ndarray) -> Optional[np.ndarray]:
+    """Stable permutation that makes the episode table policy-major, or None when it already is.  The kernel hands each
+    CTA a contiguous range of the table, so episodes of one policy run side by side on one SM and share its code in the
+    instruction cache (csrc/ks_sim_kernel.cu, work distribution)."""
+    ep_policy = np.asarray(ep_policy)
+    if ep_policy.size < 2 or np.all(ep_policy[1:] >= ep_policy[:-1]):
+        return None
+    return np.argsort(ep_policy, kind="stable")
+
+
 class BatchEvaluator:
     """Traces + one cluster resident on one GPU; evaluates batches of episodes."""
 
@@ -104,6 +114,7 @@ class BatchEvaluator:
         self._scratch = None
         self.last_plan = None
         self.last_kernel_ms = None
+        self.sm_count = torch.cuda.get_device_properties(self.device).multi_processor_count
         self.warps_per_team = 0   # 0 = planner's choice; set to force a team width
         self.ctas_per_sm = 0      # 0 = planner's choice; 1 = latency kernel, 2 = dense (throughput) kernel
 
@@ -181,10 +192,18 @@ class BatchEvaluator:
 
     # ------------------------------------------------------------------ evaluation
     def plan(self, n_episodes: int, want_placements: bool, max_pods: Optional[int] = None,
-             teams_per_block: int = 0, heap_smem_entries: int = 0, warps_per_team: int = 0) -> nat.KsPlan:
+             teams_per_block: int = 0, heap_smem_entries: int = 0, warps_per_team: int = 0,
+             episodes_per_policy: float = 1.0) -> nat.KsPlan:
+        """Launch geometry (ks_plan).  The two-CTAs-per-SM kernel is chosen for batches of several waves whose table
+        holds runs of same-policy episodes (policy-major order): warps of one SM then share a policy's code in the
+        instruction cache and the extra resident warps hide latency; with a different policy per warp they thrash it
+        (measured: +23 % on 512 policies x 16 traces, -6 % on 4,096 policies x 1 trace)."""
         p = nat.KsPlan()
         p.warps_per_team = warps_per_team or self.warps_per_team
         p.ctas_per_sm = self.ctas_per_sm
+        if p.ctas_per_sm == 0 and p.warps_per_team <= 1 and self.cluster.n_nodes <= 64 and teams_per_block == 0 \
+                and episodes_per_policy >= 8 and n_episodes >= 2 * 16 * self.sm_count:
+            p.ctas_per_sm = 2
         p.n_episodes = n_episodes
         p.n_nodes = self.cluster.n_nodes
         p.max_pods = max_pods or self.max_pods
@@ -208,8 +227,12 @@ class BatchEvaluator:
         ep_trace = np.ascontiguousarray(ep_trace, dtype=np.int32)
         if ep_policy.min() < 0 or ep_policy.max() >= len(handles) or ep_trace.min() < 0 or ep_trace.max() >= len(self.traces):
             raise ValueError("episode table refers to an unknown policy or trace")
+        order = table_order(ep_policy)
+        if order is not None:
+            ep_policy, ep_trace = np.ascontiguousarray(ep_policy[order]), np.ascontiguousarray(ep_trace[order])
         pods_per_ep = np.array([self.traces[t].n_pods for t in ep_trace], dtype=np.int64)
-        plan = self.plan(n_ep, want_placements, int(pods_per_ep.max()), teams_per_block, heap_smem_entries)
+        plan = self.plan(n_ep, want_placements, int(pods_per_ep.max()), teams_per_block, heap_smem_entries,
+                         episodes_per_policy=n_ep / len(np.unique(ep_policy)))
         self.last_plan = plan
         with torch.cuda.device(self.device):
             d_pol = torch.from_numpy(ep_policy).to(self.device)
@@ -266,6 +289,11 @@ class BatchEvaluator:
                 oc.node_index = np.where(node >= nat.KS_NODE_WAITING, -1, node)
                 oc.gpu_mask = (rec & np.uint64(0xFF)).astype(np.int64)
             out.append(oc)
+        if order is not None:   # back to the caller's episode order
+            unsorted: List[Optional[EpisodeOutcome]] = [None] * n_ep
+            for k, e in enumerate(order):
+                unsorted[int(e)] = out[k]
+            out = unsorted
         return out
 
     # ------------------------------------------------------------------ test hook: raw scores of (pod, node) cases
@@ -345,10 +373,18 @@ class ResidentBatch:
         self.ev = ev
         self.n_ep = len(ep_policy)
         self.prog = ev._program(tuple(int(p.handle) for p in policies))
+        ep_policy = np.ascontiguousarray(ep_policy, dtype=np.int32)
+        ep_trace = np.ascontiguousarray(ep_trace, dtype=np.int32)
+        self.order = table_order(ep_policy)   # the device table is policy-major; results() undoes it
+        if self.order is not None:
+            ep_policy, ep_trace = np.ascontiguousarray(ep_policy[self.order]), np.ascontiguousarray(ep_trace[self.order])
+            self.inverse = np.argsort(self.order)
+            self._d_inverse = torch.from_numpy(self.inverse).to(ev.device)
         pods_per_ep = [ev.traces[t].n_pods for t in ep_trace]
-        self.plan = ev.plan(self.n_ep, False, max(pods_per_ep), teams_per_block, heap_smem_entries)
-        self.d_pol = torch.from_numpy(np.ascontiguousarray(ep_policy, dtype=np.int32)).to(ev.device)
-        self.d_tr = torch.from_numpy(np.ascontiguousarray(ep_trace, dtype=np.int32)).to(ev.device)
+        self.plan = ev.plan(self.n_ep, False, max(pods_per_ep), teams_per_block, heap_smem_entries,
+                            episodes_per_policy=self.n_ep / len(np.unique(ep_policy)))
+        self.d_pol = torch.from_numpy(ep_policy).to(ev.device)
+        self.d_tr = torch.from_numpy(ep_trace).to(ev.device)
         self.d_res = torch.zeros(self.n_ep * nat.RESULT_DTYPE.itemsize, dtype=torch.uint8, device=ev.device)
         self.d_scratch = torch.empty(int(self.plan.scratch_bytes), dtype=torch.uint8, device=ev.device)
         b = nat.KsBatch()
@@ -372,13 +408,15 @@ class ResidentBatch:
         nat.check(self.ev.lib.ks_eval_batch(self.prog, C.byref(self.plan), C.byref(self.batch), C.c_void_p(st.cuda_stream)))
 
     def results(self) -> np.ndarray:
-        return np.frombuffer(self.d_res.cpu().numpy().tobytes(), dtype=nat.RESULT_DTYPE)
+        res = np.frombuffer(self.d_res.cpu().numpy().tobytes(), dtype=nat.RESULT_DTYPE)
+        return res if self.order is None else res[self.inverse]
 
     def scores_tensor(self):
         """Per-episode policy_score as a device fp64 tensor (a strided view of the result records)."""
         torch = self.ev._torch
         rec = self.d_res.view(torch.float64).view(self.n_ep, nat.RESULT_DTYPE.itemsize // 8)
-        return rec[:, nat.RESULT_DTYPE.fields["policy_score"][1] // 8]
+        col = rec[:, nat.RESULT_DTYPE.fields["policy_score"][1] // 8]
+        return col if self.order is None else col[self._d_inverse]
 
 
 class HostBatch:
@@ -389,8 +427,15 @@ class HostBatch:
         self.ev = ev
         self.n_ep = len(ep_policy)
         self.prog = ev._program(tuple(int(p.handle) for p in policies))
+        ep_policy = np.ascontiguousarray(ep_policy, dtype=np.int32)
+        ep_trace = np.ascontiguousarray(ep_trace, dtype=np.int32)
+        self.order = table_order(ep_policy)   # the table that crosses PCIe is policy-major; run() undoes it
+        if self.order is not None:
+            ep_policy, ep_trace = np.ascontiguousarray(ep_policy[self.order]), np.ascontiguousarray(ep_trace[self.order])
+            self.inverse = np.argsort(self.order)
         pods_per_ep = [ev.traces[t].n_pods for t in ep_trace]
-        self.plan = ev.plan(self.n_ep, False, max(pods_per_ep), teams_per_block, heap_smem_entries)
+        self.plan = ev.plan(self.n_ep, False, max(pods_per_ep), teams_per_block, heap_smem_entries,
+                            episodes_per_policy=self.n_ep / len(np.unique(ep_policy)))
 
         def pinned(a: np.ndarray):
             t = torch.from_numpy(np.ascontiguousarray(a)).pin_memory()
@@ -440,7 +485,8 @@ class HostBatch:
                                                  C.c_void_p(self.workspace.data_ptr()), self.workspace.numel(),
                                                  C.c_void_p(st.cuda_stream), C.byref(up), C.byref(down)))
         self.h2d_bytes, self.d2h_bytes = up.value, down.value
-        return np.frombuffer(self.h_res.numpy(), dtype=nat.RESULT_DTYPE)
+        res = np.frombuffer(self.h_res.numpy(), dtype=nat.RESULT_DTYPE)
+        return res if self.order is None else res[self.inverse]
 
 
 def evaluate_population(codes: Sequence[str], cluster: Optional[ClusterSpec] = None,

@@ -113,6 +113,47 @@ def test_population_sample_against_oracle(env):
         assert abs(out.policy_score - ref.score) <= 1e-9 * max(abs(ref.score), 1e-300), k
 
 
+def test_policy_major_table_and_two_ctas_per_sm(env):
+    """A trace-major episode table is replayed policy-major (same-policy episodes side by side on an SM) and, being
+    several waves long with many episodes per policy, by the two-CTAs-per-SM kernel; results come back in the caller's
+    order, identical to the one-CTA kernel's and to the oracle's."""
+    import numpy as np
+    from helpers import oracle_specs
+    from oracle import pysim
+    from funsearch_kubernetes_simulator_b200.variants import policy_population
+    from funsearch_kubernetes_simulator_b200.workload import bootstrap_trace
+    cluster = env["ClusterSpec"].load("gpu16")
+    base = env["Trace"].load("default").head(250)
+    traces = [bootstrap_trace(base, s) for s in range(128)]
+    pop = policy_population(37, seed=5)
+    ev = env["BatchEvaluator"](cluster, traces)
+    compiled = ev.compile(pop)
+    ep_pol = [p for t in range(128) for p in range(37)]
+    ep_tr = [t for t in range(128) for p in range(37)]
+    rb = ev.prepare_resident(compiled, ep_pol, ep_tr)
+    assert rb.plan.ctas_per_sm == 2 and rb.order is not None and rb.plan.blocks > ev.sm_count
+    rb.launch()
+    dense = rb.results()
+    assert (dense["status"] == 0).all()
+    ev.ctas_per_sm = 1
+    rb1 = ev.prepare_resident(compiled, ep_pol, ep_tr)
+    assert rb1.plan.ctas_per_sm == 1
+    rb1.launch()
+    one = rb1.results()
+    for f in dense.dtype.names:
+        if f not in ("device_cycles", "reserved"):
+            assert np.array_equal(dense[f], one[f]), f
+    scores = rb.scores_tensor().cpu().numpy()
+    assert np.array_equal(scores, dense["policy_score"])
+    hb = ev.prepare_host_batch(compiled, ep_pol, ep_tr)
+    assert np.array_equal(hb.run()["events"], dense["events"])
+    for e in (0, 36, 37 * 5 + 3, 37 * 127 + 36):   # the caller's order: episode e = (policy e % 37, trace e // 37)
+        cs, ts = oracle_specs(cluster, traces[ep_tr[e]])
+        ref = pysim.run_episode(cs, ts, pysim.scorer_from_source(pop[ep_pol[e]]))
+        assert (dense["events"][e], dense["attempts"][e], dense["placed"][e]) == (ref.events, ref.attempts, ref.placed), e
+        assert abs(dense["policy_score"][e] - ref.score) <= 1e-9 * max(abs(ref.score), 1e-300), e
+
+
 def test_host_buffer_entry_point_matches_resident_path(env):
     """ks_eval_batch_host (pinned host buffers) == ks_eval_batch (buffers resident in HBM)."""
     import numpy as np
