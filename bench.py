@@ -164,7 +164,7 @@ def run_b200(args):
     pop = policy_population(N_EPISODES, seed=rank)
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         cores = host_cores()
-        n_sample = max(cores, min(4 * cores, 128))
+        n_sample = max(cores, min(8 * cores, 128))   # about 30 s of CPU work on 16 cores
         p, e, t = cpu_run(pop[:n_sample], cores)
         cpu_baseline = {"value": p / t, "unit": UNIT, "cores": cores, "kind": "port",
                         "sample": f"first {n_sample} of the 1024 episodes, oracle/pysim.py on {cores} processes, {t:.1f} s",
@@ -196,9 +196,9 @@ def run_b200(args):
     ep_pol = list(range(N_EPISODES))
     ep_tr = [0] * N_EPISODES
     t0 = time.perf_counter()
-    rb = ev.prepare_resident(compiled, ep_pol, ep_tr, teams_per_block=args.teams, heap_smem_entries=args.heap_smem)
+    rb = ev.prepare_resident(compiled, ep_pol, ep_tr, teams_per_block=args.teams)
     t_link = time.perf_counter() - t0
-    hbatch = ev.prepare_host_batch(compiled, ep_pol, ep_tr, teams_per_block=args.teams, heap_smem_entries=args.heap_smem)
+    hbatch = ev.prepare_host_batch(compiled, ep_pol, ep_tr, teams_per_block=args.teams)
 
     stream = torch.cuda.current_stream(dev)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
@@ -285,8 +285,8 @@ def run_b200(args):
         peak, peak_src = json.load(open(peaks_path))["hbm_gbs"], "MEASURED_PEAKS.json hbm_gbs (measured)"
     else:
         peak, peak_src = 6650.0, "fallback 6.65 TB/s (B200_PROFILING.md)"
-    g_per_node = 8
-    alg_bytes = 32 * placed + N_EPISODES * (128 + cluster.n_nodes * (5 + 2 * g_per_node) * 4)
+    # per placement: the pod record; per episode: the result record and one read of the node constant rows
+    alg_bytes = 32 * placed + N_EPISODES * (128 + cluster.n_nodes * 20 * 4)
     achieved = alg_bytes / (kern_ms_avg * 1e-3) / 1e9
     traffic = None
     tpath = os.path.join(ROOT, "profiles", "traffic.json")
@@ -298,7 +298,7 @@ def run_b200(args):
         "dtype": "int64+f64", "data": "bundled OpenB default trace; synthetic policy population (seeded, no LLM)",
         "config": {"workload": WORKLOAD, "episodes_per_gpu": N_EPISODES, "l2": "flushed between timed steps (256 MiB write)",
                    "warps_per_team": rb.plan.warps_per_team, "teams_per_block": rb.plan.teams_per_block, "blocks": rb.plan.blocks,
-                   "heap_smem_entries": rb.plan.heap_smem_entries, "smem_per_block": rb.plan.smem_per_block,
+                   "ctas_per_sm": rb.plan.ctas_per_sm, "smem_per_block": rb.plan.smem_per_block,
                    "parity_ok_episodes": ok},
         "policy_evals_per_sec": evals_all / (ms_per_step * 1e-3),
         "events_per_sec": events_all / (ms_per_step * 1e-3),
@@ -310,7 +310,7 @@ def run_b200(args):
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                      "traffic": traffic, "peak_source": peak_src, "kernel": "ks_replay_kernel",
                      "kernel_ms_per_launch": kern_ms_avg, "algorithmic_bytes_per_launch": alg_bytes,
-                     "note": "latency/issue-bound serial event chains; HBM fraction is expected << 1% (SURVEY 8d)"},
+                     "note": "serial event chains bound by instruction fetch and dependent-issue latency (profiles/README.md); HBM fraction is expected << 1% (SURVEY 8d)"},
         "cpu_baseline": cpu_baseline,
         "compile": {"policies": N_EPISODES, "translate_and_nvrtc_s": t_compile, "link_load_s": t_link,
                     "host_cores": host_cores(), "note": "cold population, worker processes; not part of a step"},
@@ -328,7 +328,6 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--teams", type=int, default=0, help="warps (episodes) per CTA; 0 = planner's choice")
-    ap.add_argument("--heap-smem", type=int, default=0, help="event-heap entries in shared memory; 0 = planner's choice")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     if args.impl == "reference":

@@ -192,7 +192,7 @@ class BatchEvaluator:
 
     # ------------------------------------------------------------------ evaluation
     def plan(self, n_episodes: int, want_placements: bool, max_pods: Optional[int] = None,
-             teams_per_block: int = 0, heap_smem_entries: int = 0, warps_per_team: int = 0,
+             teams_per_block: int = 0, warps_per_team: int = 0,
              episodes_per_policy: float = 1.0) -> nat.KsPlan:
         """Launch geometry (ks_plan).  The two-CTAs-per-SM kernel is chosen for batches of several waves whose table
         holds runs of same-policy episodes (policy-major order): warps of one SM then share a policy's code in the
@@ -209,13 +209,12 @@ class BatchEvaluator:
         p.max_pods = max_pods or self.max_pods
         p.want_placements = 1 if want_placements else 0
         p.teams_per_block = teams_per_block
-        p.heap_smem_entries = heap_smem_entries
         nat.check(self.lib.ks_plan(C.byref(p)))
         return p
 
     def run_episodes(self, policies: Sequence[CompiledPolicy], ep_policy: Sequence[int], ep_trace: Sequence[int],
                      want_placements: bool = False, max_events: int = 0, teams_per_block: int = 0,
-                     heap_smem_entries: int = 0, stream=None) -> List[EpisodeOutcome]:
+                     stream=None) -> List[EpisodeOutcome]:
         """Evaluate episodes e = (policies[ep_policy[e]], traces[ep_trace[e]]) in one kernel launch."""
         torch = self._torch
         n_ep = len(ep_policy)
@@ -231,7 +230,7 @@ class BatchEvaluator:
         if order is not None:
             ep_policy, ep_trace = np.ascontiguousarray(ep_policy[order]), np.ascontiguousarray(ep_trace[order])
         pods_per_ep = np.array([self.traces[t].n_pods for t in ep_trace], dtype=np.int64)
-        plan = self.plan(n_ep, want_placements, int(pods_per_ep.max()), teams_per_block, heap_smem_entries,
+        plan = self.plan(n_ep, want_placements, int(pods_per_ep.max()), teams_per_block,
                          episodes_per_policy=n_ep / len(np.unique(ep_policy)))
         self.last_plan = plan
         with torch.cuda.device(self.device):
@@ -314,15 +313,15 @@ class BatchEvaluator:
 
     # ------------------------------------------------------------------ resident form (inputs already in HBM)
     def prepare_resident(self, policies: Sequence[CompiledPolicy], ep_policy: Sequence[int], ep_trace: Sequence[int],
-                         teams_per_block: int = 0, heap_smem_entries: int = 0) -> "ResidentBatch":
-        return ResidentBatch(self, policies, ep_policy, ep_trace, teams_per_block, heap_smem_entries)
+                         teams_per_block: int = 0) -> "ResidentBatch":
+        return ResidentBatch(self, policies, ep_policy, ep_trace, teams_per_block)
 
     # ------------------------------------------------------------------ host-buffer (end-to-end) form
     def prepare_host_batch(self, policies: Sequence[CompiledPolicy], ep_policy: Sequence[int], ep_trace: Sequence[int],
-                           teams_per_block: int = 0, heap_smem_entries: int = 0) -> "HostBatch":
+                           teams_per_block: int = 0) -> "HostBatch":
         """Stage a batch in pinned host memory for ks_eval_batch_host (everything the step needs crosses
         PCIe inside the call: traces, cluster table, episode table in; results out)."""
-        return HostBatch(self, policies, ep_policy, ep_trace, teams_per_block, heap_smem_entries)
+        return HostBatch(self, policies, ep_policy, ep_trace, teams_per_block)
 
     # ------------------------------------------------------------------ reference-shaped entry points
     def evaluate_population(self, codes: Sequence[str], trace_ids: Optional[Sequence[int]] = None) -> List[float]:
@@ -368,7 +367,7 @@ class ResidentBatch:
     """A batch whose episode table, result buffer and scratch already live in HBM: launch() is exactly one
     ks_eval_batch call (one memset + one kernel), nothing else."""
 
-    def __init__(self, ev: BatchEvaluator, policies, ep_policy, ep_trace, teams_per_block=0, heap_smem_entries=0):
+    def __init__(self, ev: BatchEvaluator, policies, ep_policy, ep_trace, teams_per_block=0):
         torch = ev._torch
         self.ev = ev
         self.n_ep = len(ep_policy)
@@ -381,7 +380,7 @@ class ResidentBatch:
             self.inverse = np.argsort(self.order)
             self._d_inverse = torch.from_numpy(self.inverse).to(ev.device)
         pods_per_ep = [ev.traces[t].n_pods for t in ep_trace]
-        self.plan = ev.plan(self.n_ep, False, max(pods_per_ep), teams_per_block, heap_smem_entries,
+        self.plan = ev.plan(self.n_ep, False, max(pods_per_ep), teams_per_block,
                             episodes_per_policy=self.n_ep / len(np.unique(ep_policy)))
         self.d_pol = torch.from_numpy(ep_policy).to(ev.device)
         self.d_tr = torch.from_numpy(ep_trace).to(ev.device)
@@ -422,7 +421,7 @@ class ResidentBatch:
 class HostBatch:
     """One batch held in pinned host memory + a device workspace; run() = one ks_eval_batch_host call."""
 
-    def __init__(self, ev: BatchEvaluator, policies, ep_policy, ep_trace, teams_per_block=0, heap_smem_entries=0):
+    def __init__(self, ev: BatchEvaluator, policies, ep_policy, ep_trace, teams_per_block=0):
         torch = ev._torch
         self.ev = ev
         self.n_ep = len(ep_policy)
@@ -434,7 +433,7 @@ class HostBatch:
             ep_policy, ep_trace = np.ascontiguousarray(ep_policy[self.order]), np.ascontiguousarray(ep_trace[self.order])
             self.inverse = np.argsort(self.order)
         pods_per_ep = [ev.traces[t].n_pods for t in ep_trace]
-        self.plan = ev.plan(self.n_ep, False, max(pods_per_ep), teams_per_block, heap_smem_entries,
+        self.plan = ev.plan(self.n_ep, False, max(pods_per_ep), teams_per_block,
                             episodes_per_policy=self.n_ep / len(np.unique(ep_policy)))
 
         def pinned(a: np.ndarray):

@@ -14,10 +14,10 @@ compiled = ev.compile([pol[n] for n in names])
 def run(tag, ep_pol, teams=0, S=0):
     n_ep = len(ep_pol)
     for it in range(2):
-        outs = ev.run_episodes(compiled, ep_pol, [0] * n_ep, teams_per_block=teams, heap_smem_entries=S)
+        outs = ev.run_episodes(compiled, ep_pol, [0] * n_ep, teams_per_block=teams)
     cyc = np.array([o.device_cycles for o in outs], dtype=float); evs = np.array([o.events for o in outs], dtype=float)
     p = ev.last_plan
-    print(f"{tag:46s} n_ep={n_ep:5d} teams={p.teams_per_block} blocks={p.blocks} S={p.heap_smem_entries:5d} kernel {ev.last_kernel_ms:8.2f} ms  cyc/event mean {np.mean(cyc/evs):7.0f}  placements/s {sum(o.placed for o in outs)/ev.last_kernel_ms*1e3:.3e}")
+    print(f"{tag:46s} n_ep={n_ep:5d} teams={p.teams_per_block} blocks={p.blocks} kernel {ev.last_kernel_ms:8.2f} ms  cyc/event mean {np.mean(cyc/evs):7.0f}  placements/s {sum(o.placed for o in outs)/ev.last_kernel_ms*1e3:.3e}")
 i4816 = names.index("ts_funsearch_4816"); iff = names.index("ts_first_fit"); i4901 = names.index("ts_funsearch_4901")
 run("13 policies cycled, 1024 ep", [i % len(names) for i in range(1024)])
 run("all 4816, 1024 ep", [i4816] * 1024)

@@ -17,13 +17,13 @@ t0 = time.time(); compiled = ev.compile([pol[n] for n in names]); print("compile
 ep_pol = [i % len(names) for i in range(n_ep)]
 for it in range(3):
     t0 = time.time()
-    outs = ev.run_episodes(compiled, ep_pol, [0] * n_ep, teams_per_block=teams, heap_smem_entries=S)
+    outs = ev.run_episodes(compiled, ep_pol, [0] * n_ep, teams_per_block=teams)
     wall = time.time() - t0
     placed = sum(o.placed for o in outs); evals = sum(o.scorer_calls for o in outs); events = sum(o.events for o in outs)
     ms = ev.last_kernel_ms
     p = ev.last_plan
     print(f"iter {it}: kernel {ms:.2f} ms wall {wall*1e3:.1f} ms | placements/s {placed/ms*1e3:.3e} evals/s {evals/ms*1e3:.3e} "
-          f"events/s {events/ms*1e3:.3e} | blocks {p.blocks} teams {p.teams_per_block} S {p.heap_smem_entries} smem/block {p.smem_per_block}")
+          f"events/s {events/ms*1e3:.3e} | blocks {p.blocks} teams {p.teams_per_block} smem/block {p.smem_per_block}")
 cyc = np.array([o.device_cycles for o in outs]); evs = np.array([o.events for o in outs])
 print("cycles/event: mean %.0f min %.0f max %.0f" % ((cyc/evs).mean(), (cyc/evs).min(), (cyc/evs).max()))
 for n in names:

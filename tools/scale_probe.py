@@ -36,4 +36,4 @@ if which in ("all", "many"):
         rb = ev.prepare_resident(compiled, ep, [0] * n_ep, teams_per_block=teams)
         ms = timeit(rb, 1)
         r = rb.results()
-        print(f"n_ep={n_ep:6d} ctas/sm={rb.plan.ctas_per_sm} S={rb.plan.heap_smem_entries} teams/blk={rb.plan.teams_per_block} blocks={rb.plan.blocks}: {ms:9.2f} ms  placements/s {r['placed'].sum()/ms*1e3:.3e} ok={int((r['status']==0).sum())}")
+        print(f"n_ep={n_ep:6d} ctas/sm={rb.plan.ctas_per_sm} teams/blk={rb.plan.teams_per_block} blocks={rb.plan.blocks}: {ms:9.2f} ms  placements/s {r['placed'].sum()/ms*1e3:.3e} ok={int((r['status']==0).sum())}")
