@@ -36,7 +36,7 @@ for logn in range(10, 18):
     r = rb.results()
     print(json.dumps({"config": 5, "episodes": n, "ms": ms, "placements_per_s": float(r["placed"].sum()) / ms * 1e3,
                       "policy_evals_per_s": float(r["scorer_calls"].sum()) / ms * 1e3, "episodes_per_s": n / ms * 1e3,
-                      "ok": int((r["status"] == 0).sum()), "teams_per_block": rb.plan.teams_per_block, "blocks": rb.plan.blocks}), flush=True)
+                      "ok": int((r["status"] == 0).sum()), "teams_per_block": rb.plan.teams_per_block, "blocks": rb.plan.blocks, "ctas_per_sm": rb.plan.ctas_per_sm}), flush=True)
 # ---- config 4 (one GPU's share)
 names = [t for t in available_traces() if t not in ("cpu037", "cpu072", "gpuspec05")][:16]
 traces = [bootstrap_trace(Trace.load(t), s) for t in names for s in range(4)]
@@ -52,4 +52,4 @@ fit = r["policy_score"].reshape(512, len(traces)).mean(axis=1)
 print(json.dumps({"config": 4, "episodes": len(ep_pol), "policies": 512, "traces": len(names), "seeds": 4, "ms": ms,
                   "placements_per_s": float(r["placed"].sum()) / ms * 1e3, "episodes_per_s": len(ep_pol) / ms * 1e3,
                   "status_counts": {str(k): int((r["status"] == k).sum()) for k in range(6)},
-                  "best_fitness": float(fit.max()), "mean_fitness": float(fit.mean())}), flush=True)
+                  "ctas_per_sm": rb.plan.ctas_per_sm, "best_fitness": float(fit.max()), "mean_fitness": float(fit.mean())}), flush=True)
