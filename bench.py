@@ -152,8 +152,8 @@ def run_reference(args):
 
 # --------------------------------------------------------------------------------------------- CUDA arm
 def run_b200(args):
-    if os.environ.get("NCCL_DEBUG", "").upper() in ("VERSION", ""):
-        os.environ["NCCL_DEBUG"] = "WARN"   # keep stdout to the one JSON line
+    # keep stdout to the one JSON line: NCCL writes its version banner and warnings to stdout unless given a file
+    os.environ.setdefault("NCCL_DEBUG_FILE", "/tmp/ks_bench_nccl_%h_%p.log")
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
