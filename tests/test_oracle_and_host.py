@@ -172,3 +172,31 @@ def test_plan_arithmetic(built_lib):
     assert q.blocks == 3 and q.teams_per_block == 1 and q.warps_per_team == 16 and q.smem_per_team >= 1024 * 48
     bad = nat.KsPlan()
     assert nat.lib().ks_plan(C.byref(bad)) != 0
+
+
+def test_table_order_is_a_stable_policy_major_permutation():
+    """evaluator.table_order: the permutation the evaluator applies to an episode table before upload."""
+    from funsearch_kubernetes_simulator_b200.evaluator import table_order
+    assert table_order(np.array([0, 0, 1, 2, 2])) is None and table_order(np.array([3])) is None
+    pol = np.array([2, 0, 1, 0, 2, 1, 0])
+    order = table_order(pol)
+    assert order.tolist() == [1, 3, 6, 2, 5, 0, 4]          # by policy, ties in the caller's order
+    inverse = np.argsort(order)
+    assert (pol[order][inverse] == pol).all()               # results[inverse] is back in the caller's order
+
+
+def test_plan_team_shapes(built_lib):
+    """Narrower teams may fill the 512-thread kernel on request; two CTAs per SM only with one warp per episode."""
+    from funsearch_kubernetes_simulator_b200 import _native as nat
+    p = nat.KsPlan()
+    p.n_episodes, p.n_nodes, p.max_pods, p.warps_per_team, p.teams_per_block = 296, 1024, 8152, 8, 2
+    nat.check(nat.lib().ks_plan(C.byref(p)))
+    assert p.teams_per_block == 2 and p.smem_per_block == 2 * p.smem_per_team <= 232448
+    p.teams_per_block = 3
+    assert nat.lib().ks_plan(C.byref(p)) != 0               # 24 warps do not fit a CTA
+    q = nat.KsPlan()
+    q.n_episodes, q.n_nodes, q.max_pods, q.warps_per_team, q.ctas_per_sm = 8192, 16, 8152, 2, 2
+    assert nat.lib().ks_plan(C.byref(q)) != 0
+    q.warps_per_team = 1
+    nat.check(nat.lib().ks_plan(C.byref(q)))
+    assert q.ctas_per_sm == 2 and q.blocks == 296 and q.teams_per_block == 8
