@@ -147,13 +147,11 @@ def run_reference(args):
             "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "port",
                              "sample": f"{per_step} episodes/step x {args.steps} steps of the 1024-policy population"},
             "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 # --------------------------------------------------------------------------------------------- CUDA arm
 def run_b200(args):
-    # keep stdout to the one JSON line: NCCL writes its version banner and warnings to stdout unless given a file
-    os.environ.setdefault("NCCL_DEBUG_FILE", "/tmp/ks_bench_nccl_%h_%p.log")
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
@@ -319,12 +317,28 @@ def run_b200(args):
                     "host_cores": host_cores(), "note": "cold population, worker processes; not part of a step"},
         "clocks": clocks.summary(),
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
     if world > 1:
         dist.destroy_process_group()
 
 
+_RESULT_OUT = None
+
+
+def emit(line):
+    """The one JSON line, on the process's original stdout."""
+    out = _RESULT_OUT or sys.stdout
+    out.write(json.dumps(line) + "\n")
+    out.flush()
+
+
 def main():
+    # stdout carries the JSON line only: whatever libraries print there (NCCL's version banner, worker chatter) is
+    # sent to stderr by pointing fd 1 at fd 2 for the rest of the process and its children
+    global _RESULT_OUT
+    sys.stdout.flush()
+    _RESULT_OUT = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=5)
