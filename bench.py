@@ -290,9 +290,13 @@ def run_b200(args):
     alg_bytes = 32 * placed + N_EPISODES * (128 + cluster.n_nodes * 20 * 4)
     achieved = alg_bytes / (kern_ms_avg * 1e-3) / 1e9
     traffic = None
+    ncu_issue = None
     tpath = os.path.join(ROOT, "profiles", "traffic.json")
     if os.path.exists(tpath):
-        traffic = json.load(open(tpath)).get("dram_bytes_per_launch")
+        prof = json.load(open(tpath))
+        traffic = prof.get("dram_bytes_per_launch")
+        ncu_issue = {k: prof[k] for k in ("issue_slot_utilization_pct", "threads_per_warp_instruction", "icache_hit_rate_pct",
+                                          "cycles_per_issued_instruction", "stall_no_instruction", "stall_wait") if k in prof}
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
         "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
@@ -311,6 +315,7 @@ def run_b200(args):
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                      "traffic": traffic, "peak_source": peak_src, "kernel": "ks_replay_kernel",
                      "kernel_ms_per_launch": kern_ms_avg, "algorithmic_bytes_per_launch": alg_bytes,
+                     "ncu_issue": ncu_issue,  # what actually bounds the kernel (one ncu capture, profiles/r01_f_ncu_summary.txt)
                      "note": "serial event chains bound by instruction fetch and dependent-issue latency (profiles/README.md); HBM fraction is expected << 1% (SURVEY 8d)"},
         "cpu_baseline": cpu_baseline,
         "compile": {"policies": N_EPISODES, "translate_and_nvrtc_s": t_compile, "cached_s": t_cached, "link_load_s": t_link,
