@@ -1,0 +1,22 @@
+"""Scratch: per-episode phase sums of a KS_PHASE_CLOCKS=<set> build, bench population, 1 and 7 warps per SM."""
+import os, sys
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import numpy as np, torch
+from funsearch_kubernetes_simulator_b200 import ClusterSpec, Trace, build
+build.build()
+from funsearch_kubernetes_simulator_b200.evaluator import BatchEvaluator
+from funsearch_kubernetes_simulator_b200.variants import policy_population
+names = {"1": ("pop", "score"), "2": ("fetch", "fail path"), "3": ("place path", "update+push+record")}[os.environ["KS_PHASE_CLOCKS"]]
+pop = policy_population(1024, seed=0)
+ev = BatchEvaluator(ClusterSpec.load("gpu16"), [Trace.load("default")])
+compiled = ev.compile(pop)
+for n_ep in (148, 1024):
+    rb = ev.prepare_resident(compiled, list(range(n_ep)), [0] * n_ep)
+    rb.launch(); torch.cuda.synchronize(); rb.launch(); torch.cuda.synchronize()
+    r = rb.results()
+    ev_ = r["events"].astype(float); at = r["attempts"].astype(float); placed = r["placed"].astype(float)
+    a = r["reserved"][:, 0].astype(float); b = r["reserved"][:, 1].astype(float); cyc = r["device_cycles"].astype(float)
+    fails = at - placed
+    print(f"n={n_ep}: cyc/event {np.mean(cyc/ev_):.0f} | {names[0]}: {np.mean(a/ev_):.0f}/event ({np.mean(a/np.maximum(placed,1)):.0f}/placement) | "
+          f"{names[1]}: {np.mean(b/ev_):.0f}/event ({np.mean(b/np.maximum(fails,1)):.0f}/failed attempt) | events {ev_.mean():.0f} attempts {at.mean():.0f} fails {fails.mean():.0f}", flush=True)
