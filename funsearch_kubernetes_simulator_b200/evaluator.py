@@ -130,7 +130,13 @@ class BatchEvaluator:
         from . import policy_compiler
         fresh = [s for s in dict.fromkeys(sources) if policy_compiler.cached(s) is None]
         if processes is None:
-            processes = min(os.cpu_count() or 1, 32)
+            # this process's share of the host: ranks of one torchrun launch compile their populations side by side
+            try:
+                cores = len(os.sched_getaffinity(0))
+            except AttributeError:
+                cores = os.cpu_count() or 1
+            ranks_here = max(1, int(os.environ.get("LOCAL_WORLD_SIZE", "1") or 1))
+            processes = max(1, min(cores // ranks_here, 32))
         if processes > 1 and len(fresh) >= self.POOL_THRESHOLD:
             self._compile_in_pool(fresh, processes)
         out: List[Optional[CompiledPolicy]] = []
