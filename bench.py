@@ -64,6 +64,7 @@ def cpu_run(sources, workers):
         t0 = time.perf_counter()
         out = pool.map(_cpu_episode, sources, chunksize=1)
         wall = time.perf_counter() - t0
+    _W["busy_s"] = sum(o[3] for o in out)   # summed single-core time of the episodes (for a per-core rate)
     return sum(o[0] for o in out), sum(o[1] for o in out), wall
 
 
@@ -166,7 +167,7 @@ def run_b200(args):
         p, e, t = cpu_run(pop[:n_sample], cores)
         cpu_baseline = {"value": p / t, "unit": UNIT, "cores": cores, "kind": "port",
                         "sample": f"first {n_sample} of the 1024 episodes, oracle/pysim.py on {cores} processes, {t:.1f} s",
-                        "policy_evals_per_sec": e / t}
+                        "policy_evals_per_sec": e / t, "per_core_value": p / _W["busy_s"]}
 
     import numpy as np
     import torch
