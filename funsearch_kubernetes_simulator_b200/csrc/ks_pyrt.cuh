@@ -39,6 +39,8 @@ extern "C" __device__ double ks_rt_sin(double x);
 extern "C" __device__ double ks_rt_cos(double x);
 extern "C" __device__ double ks_rt_tan(double x);
 extern "C" __device__ ks_int ks_rt_idiv(ks_int a, ks_int b);  // C truncating quotient, b != 0
+// `return max(lo, int(score))` as the scheduler wrapper sees it: int(max(0, .)) or the exception channel
+extern "C" __device__ long long ks_rt_ret_max_f2i(double score, long long lo, int st);
 
 // ------------------------------------------------------------------------------- field access
 // mutable node state: a plain shared-memory load (not volatile: the state does not change while a policy

@@ -1070,6 +1070,26 @@ class _Translator:
         self.emit("}")
         return Val(lst.ty, out)
 
+    def return_max_int_of_float(self, c) -> bool:
+        """`return max(<int literal>, int(<float expression>))` -- how the reference's template ends every policy -- is
+        finished by one shared runtime routine (ks_rt_ret_max_f2i) instead of ~25 inlined instructions per policy:
+        what is resident per policy is what the instruction cache has to hold per warp."""
+        if not (isinstance(c, ast.Call) and isinstance(c.func, ast.Name) and c.func.id == "max" and not c.keywords
+                and len(c.args) == 2 and isinstance(c.args[0], ast.Constant) and type(c.args[0].value) is int
+                and abs(c.args[0].value) < 2 ** 62 and isinstance(c.args[1], ast.Call)
+                and isinstance(c.args[1].func, ast.Name) and c.args[1].func.id == "int" and not c.args[1].keywords
+                and len(c.args[1].args) == 1 and not self.shadowed("max") and not self.shadowed("int")):
+            return False
+        saved = (list(self.lines), self.ind, self.ntmp, dict(self.seen_types), dict(self.seen_bits), set(self.need_flag),
+                 dict(self.var_types), dict(self.var_bits), set(self.defined), dict(self.static_vars))
+        x = self.expr(c.args[1].args[0])
+        if x.ty != FLOAT:   # int(int), int(bool), int(num): the general path
+            (self.lines, self.ind, self.ntmp, self.seen_types, self.seen_bits, self.need_flag, self.var_types,
+             self.var_bits, self.defined, self.static_vars) = saved
+            return False
+        self.emit(f"return ks_rt_ret_max_f2i({x.code}, {c.args[0].value}LL, st);")
+        return True
+
     def dry_type_lambda(self, key, ety, node) -> str:
         saved = (self.lines, self.ind, self.ntmp, dict(self.seen_types), dict(self.seen_bits), set(self.need_flag),
                  dict(self.var_types), dict(self.var_bits), set(self.defined), dict(self.static_vars))
@@ -1408,6 +1428,8 @@ class _Translator:
         if isinstance(s, ast.Return):
             if s.value is None:
                 self.raise_exc()  # int(max(0, None)): TypeError
+                return False
+            if self.return_max_int_of_float(s.value):
                 return False
             v = self.expr(s.value)
             if v.ty in (INT, BOOL):
