@@ -196,7 +196,8 @@ int ks_eval_batch_host(long long program, const KsPlan* plan, const KsHostBatch*
  * float_pow), which is what makes `**` in a reference policy platform-specific. */
 int ks_debug_pow(long long program, const double* x, const double* y, double* out, int n, void* stream);
 
-/* Test hook, same shape: op 0 = pow(x[i], y[i]), 1 = math.exp(x[i]), 2 = math.log(x[i]) (y unused for 1 and 2) as the
+/* Test hook, same shape: op 0 = pow(x[i], y[i]), 1 = math.exp(x[i]), 2 = math.log(x[i]) (y unused for 1 and 2),
+ * 3 = x[i] / y[i] (the shared fp64 division routine; must equal IEEE division bit for bit) as the
  * policies compute them on the device (csrc/ks_glibc_explog.h: glibc 2.39's exp and log, whole domain).  Replaces
  * CPython's calls into libm from Modules/mathmodule.c (math_exp, math_log). */
 int ks_debug_math(long long program, int op, const double* x, const double* y, double* out, int n, void* stream);

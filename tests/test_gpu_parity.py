@@ -364,6 +364,38 @@ def test_device_pow_is_bit_identical_to_host_libm(env):
     assert bad.size == 0, f"{bad.size} of {n} differ, e.g. x={x[bad[0]]!r} y={y[bad[0]]!r} got={got[bad[0]]!r} want={want[bad[0]]!r}"
 
 
+def test_device_division_is_ieee_division(env):
+    """ks_rt_ddiv (leaf fast path + out-of-line rare operands) must be IEEE-754 division bit for bit: operands of every
+    scale, subnormals, zeros, infinities, NaNs, quotients that overflow or underflow."""
+    import ctypes as C
+    import numpy as np
+    import torch
+    from funsearch_kubernetes_simulator_b200 import _native as nat
+    ev = env["BatchEvaluator"](env["ClusterSpec"].load("gpu16"), [env["Trace"].load("default").head(10)])
+    compiled = ev.compile([env["pol"]["ts_first_fit"]])
+    prog = ev._program((compiled[0].handle,))
+    rng = np.random.default_rng(21)
+    n = 1 << 20
+    q = n // 8
+    bits = lambda k: rng.integers(0, 2 ** 64, k, dtype=np.uint64).view(np.float64)           # any bit pattern
+    ints = lambda k: rng.integers(-2 ** 40, 2 ** 40, k).astype(np.float64)
+    wide = lambda k: np.ldexp(rng.random(k) + 0.5, rng.integers(-1070, 1020, k)) * rng.choice([-1.0, 1.0], k)
+    edge = np.array([0.0, -0.0, 1.0, -1.0, np.inf, -np.inf, np.nan, 5e-324, 2.2250738585072014e-308, 1.7976931348623157e308,
+                     2.0 ** -255, 2.0 ** 257, 2.0 ** -256, 2.0 ** 256, 3.0, 1 / 3])
+    x = np.concatenate([bits(q), ints(q), wide(q), rng.random(q), ints(q), wide(q), rng.random(q) * 1e6, np.repeat(edge, q // 16)])
+    y = np.concatenate([bits(q), ints(q), wide(q), rng.random(q), rng.random(q), ints(q), ints(q), np.tile(edge, q // 16)])
+    dx, dy = torch.from_numpy(x).cuda(), torch.from_numpy(y).cuda()
+    out = torch.empty_like(dx)
+    nat.check(nat.lib().ks_debug_math(prog, 3, C.c_void_p(dx.data_ptr()), C.c_void_p(dy.data_ptr()), C.c_void_p(out.data_ptr()),
+                                      len(x), C.c_void_p(torch.cuda.current_stream().cuda_stream)))
+    got = out.cpu().numpy()
+    with np.errstate(all="ignore"):
+        want = x / y
+    same = (got.view(np.uint64) == want.view(np.uint64)) | (np.isnan(got) & np.isnan(want))
+    bad = np.nonzero(~same)[0]
+    assert bad.size == 0, f"{bad.size} of {len(x)} differ, e.g. {x[bad[0]]!r} / {y[bad[0]]!r}: got {got[bad[0]]!r} want {want[bad[0]]!r}"
+
+
 def test_device_exp_log_bit_identical_to_host_libm(env):
     """math.exp / math.log in a policy are glibc's exp and log; the device versions (csrc/ks_glibc_explog.h) must return
     the same bits as this host's libm over the whole domain, overflow, subnormal results and subnormal arguments included."""
