@@ -26,6 +26,8 @@ KS_SCRATCH_HEADER = 4096
 KS_MAX_TIME = (1 << 39) - 2
 KS_STATIC_SCRATCH_BYTES = 32 << 20
 KS_PF_PREFIX_HOISTED = 1
+KS_MAX_TABLE = 4096
+KS_API_VERSION = 3
 
 # struct KsResult, 128 bytes
 RESULT_DTYPE = np.dtype([
@@ -48,7 +50,8 @@ class KsPlan(C.Structure):
 
 
 class KsBatch(C.Structure):
-    _fields_ = [("traces", C.c_void_p), ("ep_policy", C.c_void_p), ("ep_trace", C.c_void_p), ("nconst", C.c_void_p),
+    _fields_ = [("traces", C.c_void_p), ("ep_policy", C.c_void_p), ("ep_const", C.c_void_p), ("consts", C.c_void_p),
+                ("ep_trace", C.c_void_p), ("nconst", C.c_void_p),
                 ("results", C.c_void_p), ("placements", C.c_void_p), ("place_off", C.c_void_p), ("scratch", C.c_void_p),
                 ("totals", C.c_longlong * 4), ("max_events", C.c_longlong), ("snapshot_interval", C.c_double)]
 
@@ -59,7 +62,8 @@ class KsHostTrace(C.Structure):
 
 class KsHostBatch(C.Structure):
     _fields_ = [("traces", C.POINTER(KsHostTrace)), ("n_traces", C.c_int), ("reserved", C.c_int),
-                ("ep_policy", C.c_void_p), ("ep_trace", C.c_void_p), ("nconst", C.c_void_p), ("results", C.c_void_p),
+                ("ep_policy", C.c_void_p), ("ep_const", C.c_void_p), ("consts", C.c_void_p), ("n_consts", C.c_longlong),
+                ("ep_trace", C.c_void_p), ("nconst", C.c_void_p), ("results", C.c_void_p),
                 ("placements", C.c_void_p), ("place_off", C.c_void_p), ("placements_len", C.c_longlong),
                 ("totals", C.c_longlong * 4), ("max_events", C.c_longlong), ("snapshot_interval", C.c_double)]
 
@@ -95,7 +99,8 @@ _SIGNATURES = {
                                      C.c_void_p, C.POINTER(C.c_longlong), C.POINTER(C.c_longlong)]),
     "ks_debug_pow": (C.c_int, [C.c_longlong, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]),
     "ks_debug_math": (C.c_int, [C.c_longlong, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]),
-    "ks_debug_score": (C.c_int, [C.c_longlong, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "ks_debug_score": (C.c_int, [C.c_longlong, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                 C.c_void_p]),
     "ks_launch_count": (C.c_longlong, []),
     "ks_shutdown": (C.c_int, []),
 }

@@ -1,10 +1,19 @@
 """Worker processes for cold policy compilation (translation + NVRTC).
 
 NVRTC serialises much of its work inside one process (about 3x speed-up on 8 threads, measured), and the
-Python translator holds the GIL, so a population of fresh policies compiles fastest in separate processes.
-Workers translate their slice, compile it with NVRTC in groups (ks_policy_compile_many) and leave the cubins in
-the shared on-disk cache (ks_set_cache_dir); the parent then registers the same groups, which are cache hits.
-No CUDA context is touched in the workers.
+Python translator holds the GIL, so a generation of fresh policies compiles fastest in separate processes.
+A generation goes through the pool in two phases:
+
+  1. translate: the fresh SOURCES are cut into one slice per worker; each worker returns, per source, the
+     structure it translates to (CUDA text, symbol, flags) and the policy's float literals;
+  2. nvrtc: the parent keeps one copy of every structure it has not compiled yet -- a generation of 1,024
+     mutated sources is typically a few hundred structures, often far fewer -- forms groups of
+     `batch` structures (one NVRTC program each) and deals the groups to the workers, which leave the cubins in
+     the shared cache directory (ks_set_cache_dir); the parent then registers the same groups, which are cache hits.
+
+No CUDA context is touched in the workers.  They are started when the evaluator is constructed (start()), not
+inside the first evaluation, and warm themselves up (imports, mapping libnvrtc and its builtins, one trivial
+program): on a fresh box that first touch is the slowest part of the whole pipeline.
 
 The workers are plain `python -m funsearch_kubernetes_simulator_b200.compile_pool <cache_dir> <batch>`
 subprocesses talking length-prefixed pickles over stdin/stdout: unlike multiprocessing's spawn they do not
@@ -13,47 +22,66 @@ simply dropped: the parent compiles whatever is missing in-process.
 """
 from __future__ import annotations
 
+import atexit
 import ctypes as C
 import os
 import pickle
+import shutil
 import struct
 import subprocess
 import sys
 import tempfile
-from typing import List, Optional, Tuple
+import time
+from typing import List, Optional, Sequence, Tuple
 
-_WORKERS: List[subprocess.Popen] = []
+_WORKERS: List["_Worker"] = []
 _CACHE_DIR: Optional[str] = None
 _BATCH = 0
 
+# (cuda_source, symbol, flags) of one structure
+Structure = Tuple[str, str, int]
 
-def _compile_slice(sources: List[str]) -> List[Optional[Tuple[str, str, int]]]:
-    """Translate and NVRTC-compile one slice; returns (cuda_source, symbol, flags) or None per policy."""
-    from . import _native as nat
+_WARMUP_SRC = ('extern "C" __device__ long long ks_warmup_fn(KS_POLICY_PARAMS) { return ks_wrap_f(ks_div((double)p_cpu, 3.0)); }\n',
+               "ks_warmup_fn", 0)
+
+
+class _Worker:
+    def __init__(self, proc: subprocess.Popen):
+        self.proc = proc
+        self.ready = False
+        self.warmup_s: Optional[float] = None
+
+    def alive(self) -> bool:
+        return self.proc.poll() is None
+
+
+def _translate_slice(sources: Sequence[str]):
+    """Per source: (cuda_source, symbol, flags, consts) or None when it is outside the supported subset."""
     from .policy_compiler import PolicyCompileError, compile_policy
-    out: List[Optional[Tuple[str, str, int]]] = []
-    ok = []
+    out = []
     for s in sources:
         try:
             cp = compile_policy(s)
-            out.append((cp.cuda_source, cp.symbol, cp.flags))
-            ok.append(cp)
-        except PolicyCompileError:
-            out.append(None)
-    seen, uniq = set(), []
-    for cp in ok:  # distinct symbols only, in order: the parent rebuilds exactly these groups
-        if cp.symbol not in seen:
-            seen.add(cp.symbol)
-            uniq.append(cp)
-    n = len(uniq)
-    if n:
-        srcs = (C.c_char_p * n)(*[cp.cuda_source.encode() for cp in uniq])
-        syms = (C.c_char_p * n)(*[cp.symbol.encode() for cp in uniq])
-        flags = (C.c_longlong * n)(*[cp.flags for cp in uniq])
-        handles = (C.c_longlong * n)()
-        status = (C.c_int * n)()
-        nat.check(nat.lib().ks_policy_compile_many(n, srcs, syms, flags, 1, handles, status))
+            out.append((cp.cuda_source, cp.symbol, cp.flags, cp.consts))
+        except PolicyCompileError as e:
+            out.append(("error", str(e)))
     return out
+
+
+def compile_group(lib, group: Sequence[Structure]) -> Tuple[List[int], List[int]]:
+    """One NVRTC program for the structures of `group` (ks_policy_compile_many with the batch size >= len(group));
+    returns (per-structure status, per-structure handle).  Shared by the workers and by the parent's registration pass, so that both
+    form byte-identical programs and the second one is a disk-cache hit."""
+    n = len(group)
+    srcs = (C.c_char_p * n)(*[g[0].encode() for g in group])
+    syms = (C.c_char_p * n)(*[g[1].encode() for g in group])
+    flags = (C.c_longlong * n)(*[g[2] for g in group])
+    handles = (C.c_longlong * n)()
+    status = (C.c_int * n)()
+    rc = lib.ks_policy_compile_many(n, srcs, syms, flags, 1, handles, status)
+    if rc != 0:
+        return [rc] * n, [-1] * n
+    return [int(status[i]) for i in range(n)], [int(handles[i]) for i in range(n)]
 
 
 def _send(pipe, obj) -> None:
@@ -75,47 +103,104 @@ def _recv(pipe):
 
 
 def _worker_main(cache_dir: str, batch: int) -> None:
-    from . import _native as nat
-    lib = nat.lib()
-    lib.ks_set_cache_dir(cache_dir.encode())
-    lib.ks_set_compile_batch(batch)
     inp, out = sys.stdin.buffer, sys.stdout.buffer
     sys.stdout = sys.stderr  # nothing but the protocol may reach the pipe
+    t0 = time.perf_counter()
+    from . import _native as nat
+    from . import policy_compiler  # noqa: F401  (imported now, not inside the first job)
+    lib = nat.lib()
+    lib.ks_set_compile_batch(max(batch, 1))
+    # warm-up: maps libnvrtc and its builtins and runs the compiler once.  Its cubin is not cached on disk.
+    compile_group(lib, [_WARMUP_SRC])
+    lib.ks_set_cache_dir(cache_dir.encode())
+    _send(out, ("ready", time.perf_counter() - t0))
     while True:
         try:
-            job = _recv(inp)
+            kind, payload = _recv(inp)
         except EOFError:
             return
         try:
-            _send(out, ("ok", _compile_slice(job)))
+            t0 = time.perf_counter()
+            if kind == "translate":
+                res = _translate_slice(payload)
+            elif kind == "nvrtc":
+                res = [compile_group(lib, g)[0] for g in payload]
+            else:
+                raise ValueError(kind)
+            _send(out, ("ok", res, time.perf_counter() - t0))
         except Exception as exc:  # noqa: BLE001
-            _send(out, ("error", repr(exc)))
+            _send(out, ("error", repr(exc), 0.0))
 
 
-def _start(processes: int, batch: int) -> str:
-    global _CACHE_DIR, _BATCH
+def cache_dir() -> str:
+    """The cubin cache shared by the parent and its workers: RAM-backed when the box has /dev/shm."""
+    global _CACHE_DIR
     if _CACHE_DIR is None:
-        _CACHE_DIR = tempfile.mkdtemp(prefix="ks_cubin_cache_")
+        base = "/dev/shm" if os.path.isdir("/dev/shm") and os.access("/dev/shm", os.W_OK) else None
+        _CACHE_DIR = tempfile.mkdtemp(prefix="ks_cubin_cache_", dir=base)
+        atexit.register(_cleanup)
+    return _CACHE_DIR
+
+
+def _cleanup() -> None:
+    shutdown()
+    if _CACHE_DIR and os.path.isdir(_CACHE_DIR):
+        shutil.rmtree(_CACHE_DIR, ignore_errors=True)
+
+
+def start(processes: int, batch: int) -> str:
+    """Spawn workers up to `processes` (non-blocking: they warm up on their own) and return the cache directory."""
+    global _BATCH
+    d = cache_dir()
     if _BATCH != batch:
         shutdown()
         _BATCH = batch
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
     env = dict(os.environ)
     env["PYTHONPATH"] = root + os.pathsep + env.get("PYTHONPATH", "")
-    alive = [w for w in _WORKERS if w.poll() is None]
-    _WORKERS[:] = alive
+    _WORKERS[:] = [w for w in _WORKERS if w.alive()]
     while len(_WORKERS) < processes:
-        _WORKERS.append(subprocess.Popen([sys.executable, "-m", "funsearch_kubernetes_simulator_b200.compile_pool",
-                                          _CACHE_DIR, str(batch)], stdin=subprocess.PIPE, stdout=subprocess.PIPE, env=env))
-    return _CACHE_DIR
+        _WORKERS.append(_Worker(subprocess.Popen(
+            [sys.executable, "-m", "funsearch_kubernetes_simulator_b200.compile_pool", d, str(batch)],
+            stdin=subprocess.PIPE, stdout=subprocess.PIPE, env=env)))
+    return d
 
 
-def compile_slices(slices: List[List[str]], processes: int, batch: int):
-    """Compile `slices` on up to `processes` workers.  Returns (cache_dir, results) where results[i] is the list
-    _compile_slice returns for slices[i], or None when its worker failed."""
-    cache_dir = _start(min(processes, len(slices)), batch)
-    results: List[Optional[list]] = [None] * len(slices)
-    pending = list(range(len(slices)))
+def wait_ready(timeout_s: float = 300.0) -> dict:
+    """Block until every live worker has finished its warm-up; returns {"workers", "warmup_s_max"}."""
+    t_end = time.monotonic() + timeout_s
+    for w in list(_WORKERS):
+        if w.ready:
+            continue
+        try:
+            if time.monotonic() > t_end:
+                raise EOFError
+            tag, secs = _recv(w.proc.stdout)
+            if tag != "ready":
+                raise EOFError
+            w.ready, w.warmup_s = True, float(secs)
+        except (EOFError, OSError, pickle.UnpicklingError, ValueError):
+            _drop(w)
+    ws = [w.warmup_s for w in _WORKERS if w.warmup_s is not None]
+    return {"workers": len(_WORKERS), "warmup_s_max": max(ws) if ws else 0.0}
+
+
+def _drop(w: "_Worker") -> None:
+    if w in _WORKERS:
+        _WORKERS.remove(w)
+    try:
+        w.proc.kill()
+    except Exception:  # noqa: BLE001
+        pass
+
+
+def run_jobs(kind: str, jobs: List[list]):
+    """Run `jobs` (one payload each) on the pool, as many at a time as there are workers.  Returns
+    (results, worker_seconds): results[i] is the worker's answer for jobs[i] or None when its worker failed."""
+    wait_ready()
+    results: List[Optional[list]] = [None] * len(jobs)
+    secs: List[float] = [0.0] * len(jobs)
+    pending = list(range(len(jobs)))
     while pending:
         wave = []
         for w in list(_WORKERS):
@@ -123,30 +208,34 @@ def compile_slices(slices: List[List[str]], processes: int, batch: int):
                 break
             i = pending.pop(0)
             try:
-                _send(w.stdin, slices[i])
+                _send(w.proc.stdin, (kind, jobs[i]))
                 wave.append((w, i))
             except (BrokenPipeError, OSError):
-                _WORKERS.remove(w)
+                _drop(w)
         if not wave:
-            break  # no live worker: the caller compiles in-process
+            break  # no live worker: the caller does the work in-process
         for w, i in wave:
             try:
-                tag, payload = _recv(w.stdout)
+                tag, payload, dt = _recv(w.proc.stdout)
                 if tag == "ok":
                     results[i] = payload
-            except (EOFError, OSError, pickle.UnpicklingError):
-                if w in _WORKERS:
-                    _WORKERS.remove(w)
-    return cache_dir, results
+                    secs[i] = dt
+            except (EOFError, OSError, pickle.UnpicklingError, ValueError):
+                _drop(w)
+    return results, secs
+
+
+def n_workers() -> int:
+    return len([w for w in _WORKERS if w.alive()])
 
 
 def shutdown() -> None:
     for w in _WORKERS:
         try:
-            w.stdin.close()
-            w.wait(timeout=5)
+            w.proc.stdin.close()
+            w.proc.wait(timeout=5)
         except Exception:  # noqa: BLE001
-            w.kill()
+            w.proc.kill()
     _WORKERS.clear()
 
 

@@ -51,6 +51,9 @@ KS_D int ks_ns(unsigned ns, int field) {
   return v;
 }
 KS_D int ks_nc(const int* nc, int field) { return __ldg(nc + field); }
+// float literal i of the policy being evaluated (the structure's code is shared by all policies that differ only in
+// these values); a warp-uniform read-only load
+KS_D double ks_kf(const double* kf, int i) { return __ldg(kf + i); }
 // fp64 division, shared by every policy of the module (keeps the per-policy code small)
 extern "C" __device__ double ks_rt_ddiv(double a, double b);
 #ifdef KS_INLINE_DIV

@@ -7,6 +7,12 @@ generated function's return value.  The output is compiled by NVRTC (--fmad=fals
 libks_b200.so and linked with the replay kernel; arithmetic helpers live in csrc/ks_pyrt.cuh.
 
 Translation scheme
+  * a policy = a STRUCTURE + a vector of float literals: every non-zero float literal of the source becomes a read of
+    the argument `kf` (in source order), so that sources which differ only in those constants -- what most mutations
+    of a FunSearch generation change -- translate to the same CUDA text, are compiled once and share their code in the
+    SM's instruction cache; the values travel as fp64 bit patterns, so nothing is rounded or folded differently from
+    CPython (which folds nothing the translator does not).  Int literals stay structural: the bit-range tracking
+    depends on them;
   * static types: int (int64 + overflow => 'unsupported', never a silent wrap), float (fp64), bool,
     num (int-or-float decided at run time, e.g. max(0, score)), gpu (index into node.gpus), small
     lists (GPU lists, int/float lists, literal lists);
@@ -62,14 +68,35 @@ class Val:
     const: object = None                # compile-time constant value if known (int/float/bool/str)
 
 
+class _Lifted:
+    """A float literal that lives in the policy's constant vector, not in the structure's code."""
+    __slots__ = ("index", "value")
+
+    def __init__(self, index: int, value: float):
+        self.index = index
+        self.value = value
+
+
+# handle of each compiled structure (ks_policy_compile*), shared by all policies with that structure
+_STRUCT_HANDLES: Dict[str, Optional[int]] = {}
+
+
 @dataclass
 class CompiledPolicy:
     source: str
-    cuda_source: str
-    symbol: str
-    handle: Optional[int] = None
+    cuda_source: str                 # the structure's device function (identical for all policies sharing it)
+    symbol: str                      # the structure's symbol: "ks_st_" + hash of the generated code
     var_types: Dict[str, str] = field(default_factory=dict)
     flags: int = 0   # KS_PF_* (include/ks_abi.h); bit 0: the template's feasibility prefix is evaluated by the kernel
+    consts: Tuple[float, ...] = ()   # this policy's float literals, in the order the structure reads them (kf[i])
+
+    @property
+    def handle(self) -> Optional[int]:
+        return _STRUCT_HANDLES.get(self.symbol)
+
+    @handle.setter
+    def handle(self, h: Optional[int]) -> None:
+        _STRUCT_HANDLES[self.symbol] = h
 
 
 def _join(a: Optional[str], b: str) -> str:
@@ -99,7 +126,9 @@ class _Returned(Exception):
 
 class _Translator:
     def __init__(self, fn: ast.FunctionDef, consts: Dict[str, object], var_types: Dict[str, str],
-                 var_bits: Dict[str, int], flagged: set, base_bits: Optional[Dict[str, int]] = None, skip: int = 0):
+                 var_bits: Dict[str, int], flagged: set, base_bits: Optional[Dict[str, int]] = None, skip: int = 0,
+                 lift: Optional[Dict[int, int]] = None):
+        self.lift = lift or {}                  # id(ast.Constant node) -> index in the policy's constant vector
         self.base_bits = dict(base_bits or {})  # bits of each int variable's non-additive assignments (input)
         self.seen_base: Dict[str, int] = {}
         self.skip = skip                        # leading statements handled by the kernel (hoisted prefix)
@@ -255,6 +284,8 @@ class _Translator:
         raise _Returned()
 
     def const_val(self, c, node) -> Val:
+        if isinstance(c, _Lifted):
+            return Val(FLOAT, f"ks_kf(kf, {c.index})")   # a run-time value: nothing may be folded on it
         if isinstance(c, bool):
             return Val(BOOL, "1" if c else "0", bits=1, const=c)
         if isinstance(c, int):
@@ -1344,6 +1375,9 @@ class _Translator:
     # ------------------------------------------------------------------ expressions
     def expr(self, node: ast.AST) -> Val:
         if isinstance(node, ast.Constant):
+            k = self.lift.get(id(node))
+            if k is not None:
+                return Val(FLOAT, f"ks_kf(kf, {k})")
             return self.const_val(node.value, node)
         if isinstance(node, ast.Name):
             return self.lookup(node.id, node)
@@ -1674,14 +1708,44 @@ def cached(source: str) -> Optional[CompiledPolicy]:
     return _CACHE.get(hashlib.sha256(source.encode()).hexdigest())
 
 
-def adopt(source: str, cuda_source: str, symbol: str, flags: int) -> CompiledPolicy:
+def adopt(source: str, cuda_source: str, symbol: str, flags: int, consts: Tuple[float, ...] = ()) -> CompiledPolicy:
     """Register a translation produced by another process (compile_pool) under this process's cache."""
     digest = hashlib.sha256(source.encode()).hexdigest()
     cp = _CACHE.get(digest)
     if cp is None:
-        cp = CompiledPolicy(source, cuda_source, symbol, None, {}, flags)
+        cp = CompiledPolicy(source, cuda_source, symbol, {}, flags, tuple(consts))
         _CACHE[digest] = cp
     return cp
+
+
+def _is_lifted_value(c) -> bool:
+    """Float literals that go to the constant vector: all but +-0.0 (the usual `score = 0.0`, which costs nothing as
+    an immediate and which mutations leave alone)."""
+    return type(c) is float and c != 0.0
+
+
+def _lift_literals(fn: ast.FunctionDef, consts: Dict[str, object]):
+    """Numbers the float literals of the function body (document order) and of the module-level constants the
+    function can see (in order of definition).  Returns (id(node) -> index, module constants with their floats
+    replaced by _Lifted markers, the values)."""
+    values: List[float] = []
+    lift: Dict[int, int] = {}
+
+    class V(ast.NodeVisitor):
+        def visit_Constant(self, node):
+            if _is_lifted_value(node.value):
+                lift[id(node)] = len(values)
+                values.append(node.value)
+    V().visit(fn)
+
+    def mark(c):
+        if _is_lifted_value(c):
+            values.append(c)
+            return _Lifted(len(values) - 1, c)
+        if isinstance(c, (list, tuple)):
+            return type(c)(mark(x) for x in c)
+        return c
+    return lift, {k: mark(v) for k, v in consts.items()}, values
 
 
 def compile_policy(source: str) -> CompiledPolicy:
@@ -1693,7 +1757,7 @@ def compile_policy(source: str) -> CompiledPolicy:
         return hit
     try:
         tree = ast.parse(source)
-    except SyntaxError as e:
+    except (SyntaxError, ValueError, RecursionError, MemoryError) as e:
         raise PolicyCompileError(f"syntax error: {e}") from e
     fns = [s for s in tree.body if isinstance(s, ast.FunctionDef) and s.name == "priority_function"]
     if not fns:
@@ -1706,6 +1770,7 @@ def compile_policy(source: str) -> CompiledPolicy:
                           ast.NamedExpr, ast.JoinedStr, ast.Dict, ast.Set, ast.DictComp, ast.SetComp, ast.Starred)):
             raise PolicyCompileError(f"line {getattr(n, 'lineno', '?')}: {type(n).__name__} is not supported")
     consts = _module_constants(tree, fn)
+    lift, consts, kvalues = _lift_literals(fn, consts)
 
     skip = _hoistable_prefix(fn)
     var_types: Dict[str, str] = {}
@@ -1714,7 +1779,7 @@ def compile_policy(source: str) -> CompiledPolicy:
     flagged: set = set()
     tr = None
     for it in range(8):
-        tr = _Translator(fn, consts, var_types, var_bits, flagged, base_bits, skip)
+        tr = _Translator(fn, consts, var_types, var_bits, flagged, base_bits, skip, lift)
         falls = tr.run()
         new_base = dict(base_bits)
         for k, b in tr.seen_base.items():
@@ -1735,26 +1800,34 @@ def compile_policy(source: str) -> CompiledPolicy:
     else:
         raise PolicyCompileError("type inference did not converge")
 
-    symbol = "ks_pol_" + digest[:20]
-    out = [f"// translated from a priority_function(pod, node) source, sha256 {digest[:16]}",
-           f'extern "C" __device__ long long {symbol}(KS_POLICY_PARAMS) {{',
-           "  int st = 0; (void)st;",
-           "  const int ngpus = ks_nc(nc, KS_NC_NUM_GPUS); (void)ngpus;"]
+    flags = 1 if skip else 0
+    body = ["  int st = 0; (void)st;",
+            "  const int ngpus = ks_nc(nc, KS_NC_NUM_GPUS); (void)ngpus;"]
     if tr.uses_budget:
-        out.append(f"  int budget = {LOOP_BUDGET};")
+        body.append(f"  int budget = {LOOP_BUDGET};")
     for name in sorted(tr.var_types):
         ty = tr.var_types[name]
         init = {INT: "0", FLOAT: "0.0", BOOL: "0", NUM: "ks_num_i(0)", GPU: "0"}.get(ty)
         if init is None:
-            out.append(f"  {CTYPE[ty]} v_{name}; v_{name}.n = 0;")
+            body.append(f"  {CTYPE[ty]} v_{name}; v_{name}.n = 0;")
         else:
-            out.append(f"  {CTYPE[ty]} v_{name} = {init};")
+            body.append(f"  {CTYPE[ty]} v_{name} = {init};")
         if name in flagged:
-            out.append(f"  int b_{name} = 0;")
-    out.extend(tr.lines)
+            body.append(f"  int b_{name} = 0;")
+    body.extend(tr.lines)
     # reached only by falling off the end of the Python function: int(max(0, None)) raises TypeError
-    out.append("  KS_RETURN(KS_RET_EXCEPTION);")
-    out.append("}")
-    cp = CompiledPolicy(source, "\n".join(out) + "\n", symbol, None, dict(tr.var_types), 1 if skip else 0)
+    body.append("  KS_RETURN(KS_RET_EXCEPTION);")
+    body.append("}")
+    text = "\n".join(body) + "\n"
+    # the structure's name is the hash of its code: equal code <=> one device function, whatever source it came from
+    symbol = "ks_st_" + hashlib.sha256(f"{flags}|{len(kvalues)}|".encode() + text.encode()).hexdigest()[:20]
+    head = (f"// policy structure {symbol}: a priority_function(pod, node) with its {len(kvalues)} float literals in kf[]\n"
+            f'extern "C" __device__ long long {symbol}(KS_POLICY_PARAMS) {{\n')
+    cp = CompiledPolicy(source, head + text, symbol, dict(tr.var_types), flags, tuple(kvalues))
     _CACHE[digest] = cp
     return cp
+
+
+def structure_of(source: str) -> str:
+    """Name of the structure `source` translates to (raises PolicyCompileError outside the subset)."""
+    return compile_policy(source).symbol

@@ -66,15 +66,19 @@
 #define KS_POD_RESERVED 7
 #define KS_POD_INTS 8
 
-// ---- policy function ABI ---------------------------------------------------------------
-// One translated priority_function(pod, node).  The pod's fields (entities.py:30-43) travel in registers
-// (p_ctime is the retry-mutated creation_time == time of the creation event being handled); `ns` is the
+// ---- policy function ABI (v3) ----------------------------------------------------------
+// One translated priority_function(pod, node) STRUCTURE: the source with its float literals lifted out.  Policies
+// that differ only in their float constants (what most mutations of a FunSearch generation change) share one device
+// function and differ in the constant vector `kf` they are called with.  The pod's fields (entities.py:30-43) travel
+// in registers (p_ctime is the retry-mutated creation_time == time of the creation event being handled); `ns` is the
 // SHARED-memory byte address of this node's state row (field f at ns + 4 * f), `nc` points at this node's
-// row of constants in global memory (field f at nc[f]).
+// row of constants in global memory (field f at nc[f]), `kf` at the policy's float literals in source order.
 // Returns int(max(0, score)) >= 0, or KS_RET_EXCEPTION / KS_RET_UNSUPPORTED.
-#define KS_POLICY_PARAMS \
-  int p_cpu, int p_mem, int p_ngpu, int p_gmilli, long long p_ctime, long long p_dur, unsigned ns, const int *__restrict__ nc
+#define KS_POLICY_PARAMS                                                                                             \
+  int p_cpu, int p_mem, int p_ngpu, int p_gmilli, long long p_ctime, long long p_dur, unsigned ns, const int *__restrict__ nc, \
+      const double *__restrict__ kf
 typedef long long (*ks_policy_fn)(KS_POLICY_PARAMS);
+#define KS_MAX_TABLE 4096  // policy structures one linked module can dispatch to
 // flags of a dispatch-table entry
 #define KS_PF_PREFIX_HOISTED 1  // the source began with the reference template's feasibility prefix
                                 // (funsearch/safe_execution.py:204-216); the kernel evaluates it, the
@@ -117,7 +121,9 @@ struct KsResult {
 // Kernel argument block.
 struct KsLaunch {
   const KsTraceDev* traces;
-  const int* ep_policy;  // [n_episodes] slot in the linked policy table
+  const int* ep_policy;  // [n_episodes] slot in the linked policy table (the policy's structure)
+  const int* ep_const;   // [n_episodes] offset (in doubles) of the policy's float literals in `consts`; null = 0 everywhere
+  const double* consts;  // float literals of all policies of the batch (may be null when no policy has any)
   const int* ep_trace;   // [n_episodes]
   const int* nconst;     // [n_pad][KS_NC_FIELDS]
   int* work_counter;     // [gridDim.x] zeroed by the host before launch: next entry of each CTA's range of the table

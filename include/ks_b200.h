@@ -20,7 +20,7 @@
 extern "C" {
 #endif
 
-#define KS_API_VERSION 2
+#define KS_API_VERSION 3
 
 /* Error text of the last failing call on this thread.  Replaces the Python exception text the
  * reference's worker swallows (funsearch/funsearch_integration.py:63-64). */
@@ -46,8 +46,8 @@ int ks_trace_pack(long long n_pods, const int* cpu_milli, const int* memory_mib,
                   const int* gpu_milli, const long long* creation_time, const long long* duration_time,
                   const int* id_rank, int* podrec, unsigned long long* heap0, unsigned long long* place0);
 
-/* Pack a cluster into the constant node table (structure of arrays, stride n_pad = n_nodes rounded
- * up to 32) and its evaluator totals {cpu, mem, gpu count, gpu milli}.
+/* Pack a cluster into the constant node table (node-major rows of KS_NC_FIELDS ints, n_pad = n_nodes rounded
+ * up to 32 rows, rows past n_nodes zero) and its evaluator totals {cpu, mem, gpu count, gpu milli}.
  * Replaces: Cluster/Node/GPU objects (simulator/entities.py:4-26) from TraceParser.parse_nodes
  * (benchmarks/parser.py:23-61) and SchedulingEvaluator.__init__'s totals (simulator/evaluator.py:35-38).
  *   gpu_milli_total, gpu_mem_total: [n_nodes * 8] row-major, unused slots ignored
@@ -57,10 +57,11 @@ int ks_cluster_pack(int n_nodes, const int* cpu_total, const int* mem_total, con
 
 /* ---- policies --------------------------------------------------------------------------------- */
 
-/* Compile one policy, given as CUDA C source of a device function
+/* Compile one policy STRUCTURE, given as CUDA C source of a device function
  *     extern "C" __device__ long long <symbol>(KS_POLICY_PARAMS)          (include/ks_abi.h)
- * (what the Python-AST translator emits), with NVRTC for sm_100a into a relocatable cubin.  `flags` are
- * the KS_PF_* bits the dispatch table will carry for this function.  Results
+ * (what the Python-AST translator emits: the policy with its float literals lifted into the argument `kf`, so that
+ * all policies that differ only in those constants share one function), with NVRTC for sm_100a into a relocatable
+ * cubin.  `flags` are the KS_PF_* bits the dispatch table will carry for this function.  Results
  * are cached by source hash (in memory, and on disk when ks_set_cache_dir was called).
  * Replaces: FunSearchScheduler._compile_policy, exec of the policy source
  * (funsearch/funsearch_integration.py:77-89).  *policy receives a handle valid until ks_shutdown. */
@@ -80,8 +81,9 @@ const char* ks_compile_log(void);
 
 int ks_set_cache_dir(const char* path);
 
-/* Link the replay kernel with a table of policies (slot i of the table = policies[i]) and load the
- * module on the current device.  Programs are cached by their policy list.
+/* Link the replay kernel with a table of policy structures (slot i of the table = policies[i], at most KS_MAX_TABLE)
+ * and load the module on the current device.  Nothing is compiled here: the cubins are linked (nvJitLink) and the
+ * table is filled from the function addresses the loaded module reports.  Programs are cached by their policy list.
  * Replaces: handing a scorer to KubernetesSimulator(..., scheduler=...) (simulator/main.py:29-41). */
 int ks_program_link(int n_policies, const long long* policies, long long* program);
 int ks_program_release(long long program);
@@ -118,7 +120,9 @@ int ks_plan(KsPlan* plan);
  * (simulator/evaluator.py:27-164) + get_policy_score (:101-127). */
 typedef struct KsBatch {
   const KsTraceDev* traces;       /* device: table of traces */
-  const int* ep_policy;           /* device [n_episodes]: slot in the program's policy table */
+  const int* ep_policy;           /* device [n_episodes]: slot in the program's policy table (the policy's structure) */
+  const int* ep_const;            /* device [n_episodes], optional: where the policy's float literals start in consts */
+  const double* consts;           /* device, optional: the float literals of the batch's policies, back to back */
   const int* ep_trace;            /* device [n_episodes] */
   const int* nconst;              /* device: packed cluster (ks_cluster_pack) */
   KsResult* results;              /* device [n_episodes] */
@@ -144,8 +148,11 @@ int ks_eval_batch(long long program, const KsPlan* plan, const KsBatch* batch, v
  * `batch->scratch` (which is ignored and may be null); inputs and outputs are still the caller's.
  * It calls no cudaMalloc/cudaFree and no allocating library routine.
  *
- * Limit: plan->scratch_bytes must not exceed KS_STATIC_SCRATCH_BYTES, otherwise the call fails with a
- * message stating both numbers.  A plan that is too large can be shrunk by lowering plan->blocks
+ * Limit: what the plan's geometry needs -- KS_SCRATCH_HEADER + scratch_per_team x blocks x teams_per_block,
+ * recomputed inside the call, and plan->scratch_bytes, which must not understate it -- must not exceed
+ * KS_STATIC_SCRATCH_BYTES, otherwise the call fails with a message stating both numbers.  The call also fails when
+ * the current device is not the one the program was loaded on (the array lives per GPU).
+ * A plan that is too large can be shrunk by lowering plan->blocks
  * (fewer resident teams; the kernel hands out the episode table dynamically, so any block count is correct) and
  * setting plan->scratch_bytes = KS_SCRATCH_HEADER + plan->scratch_per_team * plan->blocks * plan->teams_per_block.
  *
@@ -177,6 +184,9 @@ typedef struct KsHostBatch {
   int n_traces;
   int reserved;
   const int* ep_policy;           /* host [n_episodes] */
+  const int* ep_const;            /* host [n_episodes], optional */
+  const double* consts;           /* host [n_consts], optional */
+  long long n_consts;
   const int* ep_trace;            /* host [n_episodes] */
   const int* nconst;              /* host, from ks_cluster_pack */
   KsResult* results;              /* host [n_episodes], out */
@@ -206,9 +216,9 @@ int ks_debug_math(long long program, int op, const double* x, const double* y, d
  * (pod, node) cases, obtained exactly as the replay kernel obtains it; KS_RET_EXCEPTION / KS_RET_UNSUPPORTED where the policy
  * raises / leaves the subset.  Replaces a direct call of FunSearchScheduler.__call__ (funsearch_integration.py:91-101).
  * Device pointers: pods [n][6] int64 (cpu, mem, num_gpu, gpu_milli, creation_time, duration), ns [n][KS_NS_FIELDS],
- * nc [n][KS_NC_FIELDS] (rows as in ks_abi.h), out [n]. */
-int ks_debug_score(long long program, int slot, int n, const long long* pods, const int* ns, const int* nc, long long* out,
-                   void* stream);
+ * nc [n][KS_NC_FIELDS] (rows as in ks_abi.h), kf = the policy's float literals (may be null if it has none), out [n]. */
+int ks_debug_score(long long program, int slot, int n, const long long* pods, const int* ns, const int* nc, const double* kf,
+                   long long* out, void* stream);
 
 /* Number of replay-kernel launches issued by this process so far (bench.py's gpu_launches). */
 long long ks_launch_count(void);

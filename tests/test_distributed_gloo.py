@@ -31,17 +31,23 @@ def _worker(rank, world, port, codes, costs, q):
         dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("with_costs", [False, True])
+COSTS = {"none": None, "mixed": [5.0, 1.0, 9.0, 2.0, 2.0, 7.0, 1.0],
+         # shapes that once made shards larger than the gather block (and one rank raise before the collective):
+         "zeros": [0.0, 0.0, 0.0, 0.0, 3.0, 0.0, 0.0],      # last generation's failed policies cost nothing
+         "dominant": [1e6, 1.0, 1.0, 1.0, 1.0, 1.0, 1.0]}   # one episode outweighs all others together
+
+
+@pytest.mark.parametrize("with_costs", ["none", "mixed", "zeros", "dominant"])
 def test_sharded_population_matches_single_process(with_costs):
     import torch.multiprocessing as mp
     sys.path.insert(0, ROOT)
     from funsearch_kubernetes_simulator_b200.variants import policy_population
     codes = policy_population(7, seed=2)          # odd count: ragged shards
-    costs = [5.0, 1.0, 9.0, 2.0, 2.0, 7.0, 1.0] if with_costs else None
+    costs = COSTS[with_costs]
     want = _oracle_scores(codes)
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
-    port = 29611 + (1 if with_costs else 0)
+    port = 29611 + list(COSTS).index(with_costs)
     procs = [ctx.Process(target=_worker, args=(r, 2, port, codes, costs, q)) for r in range(2)]
     for p in procs:
         p.start()
@@ -54,15 +60,21 @@ def test_sharded_population_matches_single_process(with_costs):
         assert scores == want, f"rank {rank}"
         shards[rank] = shard
     assert sorted(shards[0] + shards[1]) == list(range(7)) and not set(shards[0]) & set(shards[1])
-    if with_costs:   # LPT keeps the two ranks' loads close
+    if with_costs == "mixed":   # LPT keeps the two ranks' loads close
         load = [sum(costs[i] for i in shards[r]) for r in (0, 1)]
         assert abs(load[0] - load[1]) <= 3.0
 
 
 def test_shard_helpers_single_process():
-    from funsearch_kubernetes_simulator_b200.distributed import episode_shard, gather_scores
+    from funsearch_kubernetes_simulator_b200.distributed import episode_shard, gather_scores, shard_plan
     assert episode_shard(10, 1, 4) == [1, 5, 9]
     assert episode_shard(0, 0, 2) == []
     all_idx = sorted(sum((episode_shard(11, r, 3, list(range(11))) for r in range(3)), []))
     assert all_idx == list(range(11))
     assert gather_scores([0.5, 0.25], [1, 0], 2) == [0.25, 0.5]
+    # zero-cost items spread over the ranks instead of piling onto the lightest one
+    plan = shard_plan(64, 4, [0.0] * 30 + [float(i + 1) for i in range(34)])
+    assert sorted(sum(plan, [])) == list(range(64)) and max(len(sh) for sh in plan) - min(len(sh) for sh in plan) <= 2
+    # one dominant item: it gets a rank to itself, the others share the rest evenly
+    plan = shard_plan(64, 4, [1e6] + [1.0] * 63)
+    assert sorted(len(sh) for sh in plan) == [1, 21, 21, 21]

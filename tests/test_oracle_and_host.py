@@ -94,7 +94,7 @@ def test_library_exports_every_declared_symbol(built_lib):
         assert hasattr(lib, name), f"{name} declared in include/ks_b200.h but not exported"
     from funsearch_kubernetes_simulator_b200 import _native as nat
     assert declared == set(nat.EXPORTED_SYMBOLS)
-    assert nat.lib().ks_api_version() == 2
+    assert nat.lib().ks_api_version() == nat.KS_API_VERSION == 3
 
 
 def test_no_gpu_means_loud_failure(built_lib):

@@ -11,8 +11,9 @@ def test_shipped_policies_translate_compile_and_link(built_lib):
     from funsearch_kubernetes_simulator_b200 import _native as nat
     from funsearch_kubernetes_simulator_b200.policy_compiler import compile_policy
     _g, pol = load_golden()
-    cps = [compile_policy(src) for src in pol.values()]
-    assert len({c.symbol for c in cps}) == len(set(pol.values()))
+    every = [compile_policy(src) for src in pol.values()]
+    cps = list({c.symbol: c for c in every}.values())   # one device function per STRUCTURE
+    assert 10 <= len(cps) < len(every)
     n = len(cps)
     srcs = (C.c_char_p * n)(*[c.cuda_source.encode() for c in cps])
     syms = (C.c_char_p * n)(*[c.symbol.encode() for c in cps])
@@ -28,6 +29,27 @@ def test_shipped_policies_translate_compile_and_link(built_lib):
     again = C.c_longlong(-1)
     nat.check(nat.lib().ks_policy_compile(cps[0].cuda_source.encode(), cps[0].symbol.encode(), cps[0].flags, C.byref(again)))
     assert again.value == handles[0]
+
+
+def test_policies_that_differ_in_float_literals_share_a_structure():
+    """The float literals are lifted into the per-policy constant vector (policy ABI v3): sources that differ only in
+    them translate to the same CUDA text and symbol; int literals, operators and names are structure."""
+    from funsearch_kubernetes_simulator_b200.policy_compiler import compile_policy
+    _g, pol = load_golden()
+    a, b = compile_policy(pol["fs_random0"]), compile_policy(pol["fs_random1"])
+    assert a.symbol == b.symbol and a.cuda_source == b.cuda_source and a.consts != b.consts and len(a.consts) == 4
+    base = "def priority_function(pod, node):\n    w = [0.25, 2.5]\n    s = 0.0\n    s += node.cpu_milli_left * 1.5 + w[1]\n    return max(1, int(s * {k}))\n"
+    x, y, z = (compile_policy(base.format(k=k)) for k in ("3.0", "7.25", "3"))
+    assert x.symbol == y.symbol and x.consts == (0.25, 2.5, 1.5, 3.0) and y.consts == (0.25, 2.5, 1.5, 7.25)
+    assert z.symbol != x.symbol and z.consts == (0.25, 2.5, 1.5)          # an int literal is part of the structure
+    assert "0x" not in x.cuda_source.split("{", 1)[1].replace("0x7ff", "")  # no float literal left in the code but 0.0
+    assert compile_policy(base.format(k="3.0").replace("+ w[1]", "- w[1]")).symbol != x.symbol
+    # module-level constants are lifted too, after the function's own literals
+    m = compile_policy("ALPHA = 0.75\nBETA = [2, 0.5]\ndef priority_function(pod, node):\n    return node.gpu_left * ALPHA + BETA[1] + 1.25 + BETA[0]\n")
+    assert m.consts == (1.25, 0.75, 0.5)
+    # values that only exist as bit patterns survive the trip
+    e = compile_policy("def priority_function(pod, node):\n    return 1e999 if node.gpu_left > 5e-324 else 1.7976931348623157e308\n")
+    assert e.consts == (5e-324, float("inf"), 1.7976931348623157e308)   # AST field order: test, body, orelse
 
 
 def test_nvrtc_error_is_reported(built_lib):
@@ -87,6 +109,7 @@ def test_runtime_errors_become_exception_returns():
 
 
 def test_variant_population_is_deterministic_and_translatable():
+    from funsearch_kubernetes_simulator_b200.policy_compiler import compile_policy
     from funsearch_kubernetes_simulator_b200.variants import policy_population
     a = policy_population(64, seed=3)
     assert a == policy_population(64, seed=3) and len(set(a)) == 64

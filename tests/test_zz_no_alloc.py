@@ -90,3 +90,51 @@ def test_static_scratch_limit_and_shrunk_plan(built_lib):
     got = rb.results()
     for f in COMPARED:
         assert np.array_equal(got[f], want[f]), f
+
+
+def test_static_scratch_rejects_plans_that_understate_their_need(built_lib):
+    """The size check uses the plan's geometry, not the hand-editable scratch_bytes field: lowering scratch_bytes while
+    leaving blocks alone (half of the documented shrink recipe) must be refused, as must nonsense geometry; the call
+    never launches in these cases, so the result buffer keeps its zeros."""
+    import torch
+    from funsearch_kubernetes_simulator_b200 import _native as nat
+    ev, rb = _setup(built_lib, 8152, 600)
+    need = nat.KS_SCRATCH_HEADER + rb.plan.scratch_per_team * rb.plan.blocks * rb.plan.teams_per_block
+    assert need > nat.KS_STATIC_SCRATCH_BYTES
+    rb.d_res.zero_()
+    torch.cuda.synchronize()
+
+    def edited(**kw):
+        p = nat.KsPlan()
+        C.memmove(C.byref(p), C.byref(rb.plan), C.sizeof(nat.KsPlan))
+        for k, v in kw.items():
+            setattr(p, k, v)
+        return p
+    for tag, plan in (("scratch_bytes lowered, blocks unchanged", edited(scratch_bytes=nat.KS_STATIC_SCRATCH_BYTES)),
+                      ("negative scratch_bytes", edited(scratch_bytes=-1)),
+                      ("zero scratch_per_team", edited(scratch_per_team=0, scratch_bytes=nat.KS_SCRATCH_HEADER)),
+                      ("zero blocks", edited(blocks=0, scratch_bytes=nat.KS_SCRATCH_HEADER))):
+        rc = _static_call(ev, rb, plan)
+        assert rc != 0, tag
+        assert "ks_eval_batch_static" in nat.lib().ks_last_error().decode(), tag
+    torch.cuda.synchronize()
+    assert not rb.d_res.any().item()
+    # the caller-scratch entry point checks the same relation
+    rc = nat.lib().ks_eval_batch(rb.prog, C.byref(edited(scratch_bytes=4096)), C.byref(rb.batch),
+                                 C.c_void_p(torch.cuda.current_stream(ev.device).cuda_stream))
+    assert rc != 0 and "scratch_bytes" in nat.lib().ks_last_error().decode()
+
+
+def test_static_scratch_checks_the_device(built_lib):
+    """The array is per GPU: a call made while another device is current is refused (needs two visible GPUs)."""
+    import torch
+    from funsearch_kubernetes_simulator_b200 import _native as nat
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two visible GPUs")
+    ev, rb = _setup(built_lib, 500, 8)
+    try:
+        torch.cuda.set_device(1)
+        rc = _static_call(ev, rb)
+        assert rc != 0 and "current device" in nat.lib().ks_last_error().decode()
+    finally:
+        torch.cuda.set_device(0)
