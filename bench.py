@@ -1,21 +1,28 @@
 #!/usr/bin/env python3
-"""Headline benchmark: pod placements/s of one FunSearch generation replayed on B200(s).
+"""Headline benchmark: pod placements/s of FunSearch generations replayed on B200(s).
 
-Workload (BASELINE.json configs[1]): 1,024 policy variants x the bundled 8,152-pod OpenB trace on the
-16-node GPU cluster, one (policy, trace) episode each, per GPU ("scaling": "weak": every rank evaluates
-its own 1,024-policy population shard).  One "step" = one launch of the replay kernel over the whole
-batch (+ the NCCL all-gather of per-episode fitness when N > 1).
+Workloads (BASELINE.json configs; --config picks one, default 1):
+  1  one generation: 1,024 mutated policy variants x the bundled 8,152-pod OpenB trace x 16 nodes, one episode each,
+     per GPU ("scaling": "weak"; every rank replays the SAME population unless --population rank)
+  2  64 policies x a 1,000,000-pod synthetic Alibaba-shaped trace x 1,024 nodes (weak: every rank the same 64)
+  3  full-population fitness: P candidates x 16 traces x 4 seeds, ONE table strong-scaled over the ranks through
+     distributed.evaluate_episodes_sharded (LPT on predicted cost) with the NCCL fitness all-gather
+  4  episode-count sweep 2^10 .. 2^17 episodes of the config-1 shape (one JSON line per size)
 
-  python bench.py [--gpus N] [--steps K] [--warmup W]                 # this framework (CUDA)
-  python bench.py --impl reference [--steps K] [--warmup W]           # CPU stand-in of the reference
-  torchrun ... bench.py --gpus N ...                                   # one rank per GPU
+One "step" = one launch of the replay kernel over the whole batch (+ the NCCL all-gather of per-episode fitness
+when N > 1).
 
-Prints ONE JSON line (rank 0).  `value` = placements/s with inputs resident in HBM (CUDA events on the
-launch stream); `e2e` = the same metric through the host-buffer C-ABI call ks_eval_batch_host with the
-workload copied host->device and results device->host inside the timed region; `roofline` relates the
-algorithmic bytes (32 B per placement) to the measured HBM peak; `cpu_baseline` is the
-oracle port (oracle/pysim.py: same algorithm, CPython + heapq like the reference) on the host cores.
-NVRTC compilation of the population is reported separately under `compile` (not part of a step).
+  python bench.py [--config C] [--gpus N] [--steps K] [--warmup W]      # this framework (CUDA)
+  python bench.py --impl reference [--config C] [--steps K] [--warmup W]  # CPU stand-in of the reference
+  torchrun ... bench.py --gpus N ...                                    # one rank per GPU
+
+Prints ONE JSON line (rank 0; config 4: one per size).  `value` = placements/s with inputs resident in HBM (CUDA
+events on the launch stream); `e2e` = the same metric through the host-buffer C-ABI call ks_eval_batch_host with the
+workload copied host->device and results device->host inside the timed region; `e2e_fresh` = wall time of
+BatchEvaluator.evaluate_population on sources this process has never seen (translator, NVRTC, link, module load,
+launch, read-back all inside); `roofline` relates the algorithmic bytes (32 B per placement) to the
+measured HBM peak; `cpu_baseline` is the oracle port (oracle/pysim.py: same algorithm, CPython + heapq like the
+reference) on the host cores, and its episodes are compared with the GPU's (`parity_checked_episodes`).
 """
 import argparse
 import json
@@ -31,41 +38,63 @@ sys.path.insert(0, ROOT)
 
 METRIC = "pod_placements_per_sec"
 UNIT = "placements/s"
-N_EPISODES = 1024
-WORKLOAD = "1024 policy variants x default OpenB trace (8152 pods) x 16 nodes, 1 episode each (configs[1])"
+WORKLOADS = {
+    1: "1024 mutated policy variants x default OpenB trace (8152 pods) x 16 nodes, 1 episode each (configs[1])",
+    2: "64 policies x synthetic Alibaba-shaped trace (1,000,000 pods, load factor 200) x 1024 nodes (configs[2])",
+    3: "population x 16 bundled traces x 4 bootstrap seeds x 16 nodes, one table strong-scaled over the GPUs (configs[3])",
+    4: "episode-count sweep 2^10..2^17 episodes of the configs[1] shape (configs[4])",
+}
+
+
+def workload_config(args):
+    """The `config` object: identical in both arms (b200 / reference) for the same command line."""
+    c = {"workload": WORKLOADS[args.config], "config_id": args.config, "population": f"variants.policy_population(seed={args.seed})",
+         "population_per_rank": "same" if args.population == "same" else "seed + rank"}
+    if args.config == 3:
+        c["candidates"] = args.candidates
+    return c
 
 
 # --------------------------------------------------------------------------------------------- CPU side
 _W = {}
 
 
-def _cpu_init():
+def _cpu_init(cluster_name, n_nodes, trace_name, head):
     from funsearch_kubernetes_simulator_b200 import ClusterSpec, Trace
     sys.path.insert(0, os.path.join(ROOT, "tests"))
     from helpers import oracle_specs
-    _W["specs"] = oracle_specs(ClusterSpec.load("gpu16"), Trace.load("default"))
+    cluster = ClusterSpec.load(cluster_name)
+    if n_nodes:
+        cluster = cluster.head(n_nodes)
+    trace = Trace.load(trace_name)
+    if head:
+        trace = trace.head(head)
+    _W["specs"] = oracle_specs(cluster, trace)
 
 
 def _cpu_episode(src):
     from oracle import pysim
     cs, ts = _W["specs"]
     t0 = time.perf_counter()
-    r = pysim.run_episode(cs, ts, pysim.scorer_from_source(src))
-    return r.placed, r.scorer_calls, r.events, time.perf_counter() - t0
+    try:
+        r = pysim.run_episode(cs, ts, pysim.scorer_from_source(src))
+    except Exception:  # noqa: BLE001  (a source that does not even define the function: the worker scores it 0)
+        return 0, 0, 0, time.perf_counter() - t0, (1, 0, 0, 0, 0.0)
+    return r.placed, r.scorer_calls, r.events, time.perf_counter() - t0, (r.status, r.events, r.attempts, r.placed, r.score)
 
 
-def cpu_run(sources, workers):
-    """Replays `sources` on the default workload with the oracle port on `workers` processes.
-    Returns (placements, scorer_calls, wall seconds)."""
+def cpu_run(sources, workers, spec=("gpu16", 0, "default", 0)):
+    """Replays `sources` on one workload with the oracle port on `workers` processes.
+    Returns (placements, scorer_calls, wall seconds, per-episode (status, events, attempts, placed, score))."""
     import multiprocessing as mp
     ctx = mp.get_context("spawn")
-    with ctx.Pool(workers, initializer=_cpu_init) as pool:
+    with ctx.Pool(workers, initializer=_cpu_init, initargs=spec) as pool:
         pool.map(_cpu_episode, sources[:workers])  # warm the workers (imports, trace load)
         t0 = time.perf_counter()
         out = pool.map(_cpu_episode, sources, chunksize=1)
         wall = time.perf_counter() - t0
     _W["busy_s"] = sum(o[3] for o in out)   # summed single-core time of the episodes (for a per-core rate)
-    return sum(o[0] for o in out), sum(o[1] for o in out), wall
+    return sum(o[0] for o in out), sum(o[1] for o in out), wall, [o[4] for o in out]
 
 
 def host_cores():
@@ -119,6 +148,37 @@ class ClockSampler:
                 "reasons": sorted(reasons), "samples": len(self.rows)}
 
 
+# --------------------------------------------------------------------------------------------- workloads
+def build_workload(args, rank, world):
+    """(cluster, traces, sources, ep_policy, ep_trace, cpu_spec) for this rank.  Weak-scaled configs give every rank
+    its own full table; config 3 gives every rank the WHOLE table (the sharded API cuts it)."""
+    from funsearch_kubernetes_simulator_b200 import ClusterSpec, Trace, bootstrap_trace, synthetic_trace
+    from funsearch_kubernetes_simulator_b200.variants import policy_population
+    seed = args.seed + (rank if args.population == "rank" else 0)
+    if args.config in (1, 4):
+        cluster, traces = ClusterSpec.load("gpu16"), [Trace.load("default")]
+        n = args.episodes or 1024
+        pop = policy_population(min(n, 1024), seed=seed)
+        ep_pol = [i % len(pop) for i in range(n)]
+        ep_tr = [0] * n
+        return cluster, traces, pop, ep_pol, ep_tr, ("gpu16", 0, "default", 0)
+    if args.config == 2:
+        cluster = ClusterSpec.load("all1523").head(1024)
+        traces = [synthetic_trace(args.pods or 1000000, seed=3, load_factor=200.0)]
+        pop = policy_population(64, seed=seed)
+        return cluster, traces, pop, list(range(64)), [0] * 64, None
+    if args.config == 3:
+        cluster = ClusterSpec.load("gpu16")
+        names = ["default", "cpu037", "cpu050", "cpu072", "cpu100", "cpu200", "cpu235", "cpu250", "cpu300", "gpushare20",
+                 "gpushare40", "gpushare60", "gpushare80", "gpushare100", "gpuspec10", "gpuspec25"]
+        traces = [bootstrap_trace(Trace.load(nm), s) for nm in names for s in range(4)]
+        pop = policy_population(args.candidates, seed=args.seed)
+        ep_pol = [p for p in range(len(pop)) for _t in range(len(traces))]
+        ep_tr = [t for _p in range(len(pop)) for t in range(len(traces))]
+        return cluster, traces, pop, ep_pol, ep_tr, None
+    raise ValueError(args.config)
+
+
 # --------------------------------------------------------------------------------------------- reference arm
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
@@ -126,7 +186,11 @@ def run_reference(args):
         return
     from funsearch_kubernetes_simulator_b200.variants import policy_population
     cores = host_cores()
-    pop = policy_population(N_EPISODES, seed=0)
+    if args.config != 1:
+        emit({"impl": "reference", "metric": METRIC, "unit": UNIT, "config": workload_config(args),
+              "unavailable": "the CPU arm is timed on configs[1]; configs 2-4 carry their own bounded CPU column in cpu_baseline"})
+        return
+    pop = policy_population(1024, seed=args.seed)
     per_step = max(cores, min(4 * cores, 1024))
     for w in range(max(0, min(args.warmup, 1))):
         cpu_run(pop[:cores], cores)
@@ -134,16 +198,17 @@ def run_reference(args):
     wall = 0.0
     for k in range(args.steps):
         sample = [pop[(k * per_step + i) % len(pop)] for i in range(per_step)]
-        p, e, t = cpu_run(sample, cores)
+        p, e, t, _ = cpu_run(sample, cores)
         placed += p
         evals += e
         wall += t
     v = placed / wall
     line = {"impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": wall / args.steps * 1e3, "higher_is_better": True, "scaling": "weak",
-            "vs_baseline": None, "dtype": "int64+f64", "data": "bundled OpenB default trace; synthetic policy population (seed 0)",
-            "config": {"workload": WORKLOAD, "note": "CPU stand-in of the reference's own path: oracle/pysim.py "
-                       "(CPython + heapq, exec'd policies) on all host cores; /root/reference cannot travel to the GPU box"},
+            "vs_baseline": None, "dtype": "int64+f64", "data": "bundled OpenB default trace; synthetic policy population (seeded, no LLM)",
+            "config": workload_config(args),
+            "note": "CPU stand-in of the reference's own path: oracle/pysim.py (CPython + heapq, exec'd policies) on all host "
+                    "cores; /root/reference cannot travel to the GPU box (BASELINE.md: the port runs 1.28x faster than the reference)",
             "policy_evals_per_sec": evals / wall,
             "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "port",
                              "sample": f"{per_step} episodes/step x {args.steps} steps of the 1024-policy population"},
@@ -156,25 +221,30 @@ def run_b200(args):
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
-    from funsearch_kubernetes_simulator_b200.variants import policy_population
+    t_gen = time.perf_counter()
+    cluster, traces, pop, ep_pol, ep_tr, cpu_spec = build_workload(args, rank, world)
+    t_gen = time.perf_counter() - t_gen
+    n_ep = len(ep_pol)
 
-    # CPU baseline first (rank 0, N == 1): processes are spawned before CUDA is touched
+    # CPU baseline first (rank 0, N == 1): processes are spawned before CUDA is touched.  Its episodes are kept:
+    # they are compared with the GPU's results for the same (policy, trace) pairs below.
     cpu_baseline = None
-    pop = policy_population(N_EPISODES, seed=rank)
-    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+    cpu_rows = []
+    n_sample = 0
+    if rank == 0 and world == 1 and not args.no_cpu_baseline and cpu_spec is not None:
         cores = host_cores()
-        n_sample = max(cores, min(8 * cores, 128))   # about 30 s of CPU work on 16 cores
-        p, e, t = cpu_run(pop[:n_sample], cores)
+        n_sample = min(n_ep, max(cores, min(8 * cores, 128)))   # about 30 s of CPU work on 16 cores
+        p, e, t, cpu_rows = cpu_run([pop[ep_pol[i]] for i in range(n_sample)], cores, cpu_spec)
         cpu_baseline = {"value": p / t, "unit": UNIT, "cores": cores, "kind": "port",
-                        "sample": f"first {n_sample} of the 1024 episodes, oracle/pysim.py on {cores} processes, {t:.1f} s",
+                        "sample": f"first {n_sample} of the {n_ep} episodes, oracle/pysim.py on {cores} processes, {t:.1f} s",
                         "policy_evals_per_sec": e / t, "per_core_value": p / _W["busy_s"]}
 
     import numpy as np
     import torch
     import torch.distributed as dist
-    from funsearch_kubernetes_simulator_b200 import ClusterSpec, Trace
     from funsearch_kubernetes_simulator_b200 import _native as nat
     from funsearch_kubernetes_simulator_b200.evaluator import BatchEvaluator
+    from funsearch_kubernetes_simulator_b200 import compile_pool
     import __graft_entry__
     if rank == 0:
         __graft_entry__.build()
@@ -183,20 +253,23 @@ def run_b200(args):
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
         dist.barrier()
     dev = torch.device("cuda", local)
-    cluster, trace = ClusterSpec.load("gpu16"), Trace.load("default")
-    ev = BatchEvaluator(cluster, [trace], device=local)
+    t0 = time.perf_counter()
+    ev = BatchEvaluator(cluster, traces, device=local)
+    pool_info = compile_pool.wait_ready() if compile_pool.n_workers() else {"workers": 0, "warmup_s_max": 0.0}
+    t_pool = time.perf_counter() - t0
 
     from funsearch_kubernetes_simulator_b200 import policy_compiler
-    policy_compiler._CACHE.clear()   # policy_population() already translated them once: time a cold compilation
+    policy_compiler._CACHE.clear()   # the generator does not translate, but be explicit: time a cold compilation
     t0 = time.perf_counter()
-    compiled = ev.compile(pop)       # translation + NVRTC, in worker processes for a population this large
+    compiled = ev.compile(pop)       # translation + NVRTC of the new structures, in worker processes
     t_compile = time.perf_counter() - t0
-    assert all(c is not None for c in compiled)
+    cstats = dict(ev.last_compile_stats)
+    untranslated = [i for i, c in enumerate(compiled) if c is None]
+    assert not untranslated, f"{len(untranslated)} sources of the population do not translate, e.g. #{untranslated[0]}: " \
+                             f"{ev.compile_error(pop[untranslated[0]])}"
     t0 = time.perf_counter()
-    ev.compile(pop)                  # the same sources again: translator cache + cubin cache
+    ev.compile(pop)                  # the same sources again: translator cache + registered structures
     t_cached = time.perf_counter() - t0
-    ep_pol = list(range(N_EPISODES))
-    ep_tr = [0] * N_EPISODES
     t0 = time.perf_counter()
     rb = ev.prepare_resident(compiled, ep_pol, ep_tr, teams_per_block=args.teams)
     t_link = time.perf_counter() - t0
@@ -204,7 +277,7 @@ def run_b200(args):
 
     stream = torch.cuda.current_stream(dev)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
-    gathered = torch.empty(world * N_EPISODES, dtype=torch.float64, device=dev) if world > 1 else None
+    gathered = torch.empty(world * n_ep, dtype=torch.float64, device=dev) if world > 1 else None
 
     def step():
         rb.launch(stream)
@@ -243,6 +316,22 @@ def run_b200(args):
     events = int(res["events"].sum())
     ok = int((res["status"] == 0).sum())
     total_ms = float(sum(step_ms))
+    cyc = res["device_cycles"].astype(np.float64)
+
+    # parity of the measured workload: the CPU leg's episodes against the GPU's
+    parity_checked = parity_bad = 0
+    first_bad = None
+    for i, row in enumerate(cpu_rows):
+        g = res[i]
+        got = (int(g["status"]), int(g["events"]), int(g["attempts"]), int(g["placed"]))
+        same = got == tuple(row[:4]) and abs(float(g["policy_score"]) - row[4]) <= 1e-9 * max(abs(row[4]), 1e-300)
+        if row[0] != 0:   # a failed episode: the status and a zero score are what must agree
+            same = got[0] == row[0] and float(g["policy_score"]) == 0.0
+        parity_checked += 1
+        if not same:
+            parity_bad += 1
+            if first_bad is None:
+                first_bad = {"episode": i, "gpu": got + (float(g["policy_score"]),), "cpu": list(row)}
 
     # end to end through the host-buffer C ABI
     for _ in range(2):
@@ -260,6 +349,31 @@ def run_b200(args):
     e2e_s = time.perf_counter() - t0
     e2e_placed = int(hres["placed"].sum())
     assert e2e_placed == placed, "host-buffer path and resident path disagree"
+
+    # a fresh generation end to end through the reference-shaped call: sources never seen by this process
+    fresh = None
+    if args.fresh_steps > 0 and args.config == 1:
+        from funsearch_kubernetes_simulator_b200.variants import policy_population
+        gens = [policy_population(1024, seed=100003 + 7919 * (k + 1) + rank) for k in range(args.fresh_steps + 1)]
+        walls, stats, placed_f, structs, not_eval = [], [], [], [], []
+        for k, g in enumerate(gens):
+            if world > 1:
+                dist.barrier()
+            t0 = time.perf_counter()
+            ev.evaluate_population(g)           # translate + NVRTC + link + load + launch + read-back
+            dt = time.perf_counter() - t0
+            if k == 0:
+                continue                        # untimed warm-up generation (first use of the linker etc.)
+            walls.append(dt)
+            stats.append(dict(ev.last_compile_stats))
+            structs.append(ev.last_report.distinct_structures)
+            not_eval.append(len(ev.last_report.not_evaluated))
+            placed_f.append(8152 * sum(1 for s in ev.last_report.status if s == 0))
+        fresh = {"value": sum(placed_f) / sum(walls), "unit": UNIT, "ms_per_generation": [round(w * 1e3, 1) for w in walls],
+                 "generations": len(walls), "policies_per_generation": 1024, "distinct_structures": structs,
+                 "not_evaluated": not_eval, "stages": stats,
+                 "path": "BatchEvaluator.evaluate_population(sources): translate + NVRTC of new structures (worker pool) + "
+                         "nvJitLink + module load + H2D + kernel + D2H; one untimed warm-up generation before"}
 
     # aggregate over ranks: max time, summed work
     stats = torch.tensor([total_ms, e2e_s, float(placed), float(evals), float(events), float(sum(kern_ms))],
@@ -287,40 +401,53 @@ def run_b200(args):
         peak, peak_src = json.load(open(peaks_path))["hbm_gbs"], "MEASURED_PEAKS.json hbm_gbs (measured)"
     else:
         peak, peak_src = 6650.0, "fallback 6.65 TB/s (B200_PROFILING.md)"
-    # per placement: the pod record; per episode: the result record and one read of the node constant rows
-    alg_bytes = 32 * placed + N_EPISODES * (128 + cluster.n_nodes * 20 * 4)
+    # per placement: the pod record + placement record; per episode: the result record and one read of the node constant rows
+    alg_bytes = 32 * placed + n_ep * (128 + cluster.n_nodes * 20 * 4)
     achieved = alg_bytes / (kern_ms_avg * 1e-3) / 1e9
     traffic = None
     ncu_issue = None
     tpath = os.path.join(ROOT, "profiles", "traffic.json")
-    if os.path.exists(tpath):
+    if os.path.exists(tpath) and args.config == 1:
         prof = json.load(open(tpath))
         traffic = prof.get("dram_bytes_per_launch")
         ncu_issue = {k: prof[k] for k in ("issue_slot_utilization_pct", "threads_per_warp_instruction", "icache_hit_rate_pct",
                                           "cycles_per_issued_instruction", "stall_no_instruction", "stall_wait") if k in prof}
+    cfg = workload_config(args)
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
         "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "int64+f64", "data": "bundled OpenB default trace; synthetic policy population (seeded, no LLM)",
-        "config": {"workload": WORKLOAD, "episodes_per_gpu": N_EPISODES, "l2": "flushed between timed steps (256 MiB write)",
+        "config": cfg,
+        "launch": {"episodes_per_gpu": n_ep, "l2": "flushed between timed steps (256 MiB write)",
                    "warps_per_team": rb.plan.warps_per_team, "teams_per_block": rb.plan.teams_per_block, "blocks": rb.plan.blocks,
                    "ctas_per_sm": rb.plan.ctas_per_sm, "smem_per_block": rb.plan.smem_per_block,
-                   "parity_ok_episodes": ok},
+                   "distinct_structures": rb.n_structures, "distinct_sources": len(set(pop)),
+                   "status_ok_episodes": ok,
+                   "slowest_episode_mcycles": float(cyc.max() / 1e6), "mean_episode_mcycles": float(cyc.mean() / 1e6)},
+        "parity_checked_episodes": parity_checked, "parity_mismatches": parity_bad, "parity_first_mismatch": first_bad,
         "policy_evals_per_sec": evals_all / (ms_per_step * 1e-3),
         "events_per_sec": events_all / (ms_per_step * 1e-3),
-        "episodes_per_sec": N_EPISODES * world / (ms_per_step * 1e-3),
+        "episodes_per_sec": n_ep * world / (ms_per_step * 1e-3),
         "e2e": {"value": placed_all / (e2e_s / args.steps), "unit": UNIT, "h2d_bytes_per_step": hbatch.h2d_bytes,
                 "d2h_bytes_per_step": hbatch.d2h_bytes, "ms_per_step": e2e_s / args.steps * 1e3,
                 "path": "ks_eval_batch_host (pinned host buffers -> device workspace -> kernel -> host results)"},
+        "e2e_fresh": fresh,
         "gpu_launches": int(launches),
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                     "traffic": traffic, "peak_source": peak_src, "kernel": "ks_replay_kernel",
+                     "traffic": traffic,
+                     "traffic_source": "replayed from profiles/traffic.json (one ncu --set full capture of this command by the builder), not measured in this run" if traffic else None,
+                     "peak_source": peak_src, "kernel": "ks_replay_kernel",
                      "kernel_ms_per_launch": kern_ms_avg, "algorithmic_bytes_per_launch": alg_bytes,
-                     "ncu_issue": ncu_issue,  # what actually bounds the kernel (one ncu capture, profiles/r01_f_ncu_summary.txt)
+                     "ncu_issue": ncu_issue,
                      "note": "serial event chains bound by instruction fetch and dependent-issue latency (profiles/README.md); HBM fraction is expected << 1% (SURVEY 8d)"},
         "cpu_baseline": cpu_baseline,
-        "compile": {"policies": N_EPISODES, "translate_and_nvrtc_s": t_compile, "cached_s": t_cached, "link_load_s": t_link,
-                    "host_cores": host_cores(), "note": "cold population, worker processes; not part of a step"},
+        "compile": {"policies": len(pop), "distinct_structures": cstats.get("new_structures"), "total_s": t_compile,
+                    "translate_s": cstats.get("translate_s"), "nvrtc_s": cstats.get("nvrtc_s"), "register_s": cstats.get("register_s"),
+                    "worker_translate_s_max": cstats.get("worker_translate_s_max"), "worker_nvrtc_s_max": cstats.get("worker_nvrtc_s_max"),
+                    "cached_s": t_cached, "link_load_s": t_link, "pool_workers": pool_info["workers"],
+                    "pool_warmup_s_max": pool_info["warmup_s_max"], "evaluator_and_pool_ready_s": t_pool,
+                    "population_generation_s": t_gen, "host_cores": host_cores(),
+                    "note": "cold population, worker processes; not part of a step (e2e_fresh is the number that includes it)"},
         "clocks": clocks.summary(),
     }
     emit(line)
@@ -350,6 +477,14 @@ def main():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--config", type=int, default=1, choices=[1, 2, 3, 4])
+    ap.add_argument("--seed", type=int, default=0)
+    ap.add_argument("--population", default="same", choices=["same", "rank"],
+                    help="weak scaling: every rank replays the same population (default) or its own (seed + rank)")
+    ap.add_argument("--episodes", type=int, default=0, help="configs 1/4: episodes per GPU (default 1024)")
+    ap.add_argument("--pods", type=int, default=0, help="config 2: pods of the synthetic trace (default 1,000,000)")
+    ap.add_argument("--candidates", type=int, default=1024, help="config 3: policies in the population")
+    ap.add_argument("--fresh-steps", type=int, default=2, help="timed fresh generations for e2e_fresh (0 = skip)")
     ap.add_argument("--teams", type=int, default=0, help="warps (episodes) per CTA; 0 = planner's choice")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()

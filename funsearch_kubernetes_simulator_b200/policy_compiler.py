@@ -66,6 +66,7 @@ class Val:
     items: Optional[list] = None        # STATIC: element Vals
     node: Optional[ast.AST] = None      # LAMBDA
     const: object = None                # compile-time constant value if known (int/float/bool/str)
+    lit: Optional[tuple] = None         # (ast.Constant node, sign) when this is an int literal of the source
 
 
 class _Lifted:
@@ -127,8 +128,11 @@ class _Returned(Exception):
 class _Translator:
     def __init__(self, fn: ast.FunctionDef, consts: Dict[str, object], var_types: Dict[str, str],
                  var_bits: Dict[str, int], flagged: set, base_bits: Optional[Dict[str, int]] = None, skip: int = 0,
-                 lift: Optional[Dict[int, int]] = None):
-        self.lift = lift or {}                  # id(ast.Constant node) -> index in the policy's constant vector
+                 lift: Optional[Dict[int, int]] = None, kvalues: Optional[List[float]] = None,
+                 ilift: Optional[Dict[tuple, int]] = None):
+        self.ilift = ilift if ilift is not None else {}   # (id(int literal node), sign) -> index, assigned on first use
+        self.lift = lift if lift is not None else {}   # id(ast.Constant node) -> index in the policy's constant vector
+        self.kvalues = kvalues if kvalues is not None else []   # the vector itself (grows when an int literal is lifted)
         self.base_bits = dict(base_bits or {})  # bits of each int variable's non-additive assignments (input)
         self.seen_base: Dict[str, int] = {}
         self.skip = skip                        # leading statements handled by the kernel (hoisted prefix)
@@ -204,6 +208,17 @@ class _Translator:
             return v.code
         if v.ty in (INT, BOOL):
             if v.const is not None:
+                if v.ty == INT and v.lit is not None and 2 < abs(int(v.const)) < (1 << 53):
+                    # An int literal used where a float is needed (`u * 100`, `score -= 20`, `x > 50` with float u,
+                    # score, x): CPython converts it exactly, so float(literal) can live in the constant vector like
+                    # a float literal, and policies that differ in such coefficients still share a structure.
+                    # (Ints that stay ints are structure: the bit-range tracking depends on their values.)
+                    key = (id(v.lit[0]), v.lit[1])   # kept apart from the float literals' ids: an int literal is
+                    k = self.ilift.get(key)          # only lifted where it is used as a float
+                    if k is None:
+                        k = self.ilift[key] = len(self.kvalues)
+                        self.kvalues.append(float(int(v.const)))
+                    return f"ks_kf(kf, {k})"
                 return _flit(float(int(v.const)))
             return f"ks_i2d((ks_int){v.code})" if v.bits > 53 else f"(double){v.code}"
         if v.ty == NUM:
@@ -292,7 +307,8 @@ class _Translator:
             if abs(c) >= 1 << 63:
                 self.fail(node, "integer literal beyond int64")
             code = f"{c}LL" if c > -(1 << 63) else "(-9223372036854775807LL-1)"
-            return Val(INT, f"({code})" if c < 0 else code, bits=max(1, abs(c).bit_length()), const=c)
+            lit = (node, 1) if isinstance(node, ast.Constant) and node.value is c else None
+            return Val(INT, f"({code})" if c < 0 else code, bits=max(1, abs(c).bit_length()), const=c, lit=lit)
         if isinstance(c, float):
             return Val(FLOAT, f"({_flit(c)})", const=c)
         if c is None:
@@ -1400,7 +1416,10 @@ class _Translator:
                 if v.ty in (INT, BOOL):
                     v = self.as_int(v)
                     if v.const is not None:
-                        return self.const_val(-int(v.const), node)
+                        r = self.const_val(-int(v.const), node)
+                        if v.lit is not None and v.lit[1] == 1:   # `-5`: still a literal of the source
+                            r.lit = (v.lit[0], -1)
+                        return r
                     if v.bits <= 62:
                         return self.tmp(INT, f"-{v.code}", bits=v.bits)
                     r = self.tmp(INT, f"ks_ineg({v.code}, &st)")
@@ -1771,6 +1790,7 @@ def compile_policy(source: str) -> CompiledPolicy:
             raise PolicyCompileError(f"line {getattr(n, 'lineno', '?')}: {type(n).__name__} is not supported")
     consts = _module_constants(tree, fn)
     lift, consts, kvalues = _lift_literals(fn, consts)
+    ilift: Dict[tuple, int] = {}
 
     skip = _hoistable_prefix(fn)
     var_types: Dict[str, str] = {}
@@ -1779,7 +1799,7 @@ def compile_policy(source: str) -> CompiledPolicy:
     flagged: set = set()
     tr = None
     for it in range(8):
-        tr = _Translator(fn, consts, var_types, var_bits, flagged, base_bits, skip, lift)
+        tr = _Translator(fn, consts, var_types, var_bits, flagged, base_bits, skip, lift, kvalues, ilift)
         falls = tr.run()
         new_base = dict(base_bits)
         for k, b in tr.seen_base.items():
