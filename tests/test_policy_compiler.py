@@ -41,7 +41,9 @@ def test_policies_that_differ_in_float_literals_share_a_structure():
     base = "def priority_function(pod, node):\n    w = [0.25, 2.5]\n    s = 0.0\n    s += node.cpu_milli_left * 1.5 + w[1]\n    return max(1, int(s * {k}))\n"
     x, y, z = (compile_policy(base.format(k=k)) for k in ("3.0", "7.25", "3"))
     assert x.symbol == y.symbol and x.consts == (0.25, 2.5, 1.5, 3.0) and y.consts == (0.25, 2.5, 1.5, 7.25)
-    assert z.symbol != x.symbol and z.consts == (0.25, 2.5, 1.5)          # an int literal is part of the structure
+    assert z.symbol == x.symbol and z.consts == x.consts    # an int literal used as a float (s * 3) is lifted as 3.0
+    i0, i1 = (compile_policy(base.format(k="3.0").replace("s * 3.0", f"s * 3.0 + pod.num_gpu * {m}")) for m in (4, 5))
+    assert i0.symbol != i1.symbol and i0.consts == i1.consts                # an int that stays an int is structure
     assert "0x" not in x.cuda_source.split("{", 1)[1].replace("0x7ff", "")  # no float literal left in the code but 0.0
     assert compile_policy(base.format(k="3.0").replace("+ w[1]", "- w[1]")).symbol != x.symbol
     # module-level constants are lifted too, after the function's own literals
