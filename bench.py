@@ -271,9 +271,10 @@ def run_b200(args):
     ev.compile(pop)                  # the same sources again: translator cache + registered structures
     t_cached = time.perf_counter() - t0
     t0 = time.perf_counter()
-    rb = ev.prepare_resident(compiled, ep_pol, ep_tr, teams_per_block=args.teams)
+    single = True if args.single_module else None
+    rb = ev.prepare_resident(compiled, ep_pol, ep_tr, teams_per_block=args.teams, single_module=single)
     t_link = time.perf_counter() - t0
-    hbatch = ev.prepare_host_batch(compiled, ep_pol, ep_tr, teams_per_block=args.teams)
+    hbatch = ev.prepare_host_batch(compiled, ep_pol, ep_tr, teams_per_block=args.teams, single_module=single)
 
     stream = torch.cuda.current_stream(dev)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
@@ -442,9 +443,11 @@ def run_b200(args):
                      "note": "serial event chains bound by instruction fetch and dependent-issue latency (profiles/README.md); HBM fraction is expected << 1% (SURVEY 8d)"},
         "cpu_baseline": cpu_baseline,
         "compile": {"policies": len(pop), "distinct_structures": cstats.get("new_structures"), "total_s": t_compile,
-                    "translate_s": cstats.get("translate_s"), "nvrtc_s": cstats.get("nvrtc_s"), "register_s": cstats.get("register_s"),
-                    "worker_translate_s_max": cstats.get("worker_translate_s_max"), "worker_nvrtc_s_max": cstats.get("worker_nvrtc_s_max"),
-                    "cached_s": t_cached, "link_load_s": t_link, "pool_workers": pool_info["workers"],
+                    "translate_s": cstats.get("translate_s"), "nvrtc_link_s": cstats.get("nvrtc_link_s"),
+                    "register_load_s": cstats.get("register_load_s"), "modules_loaded": cstats.get("modules_loaded"),
+                    "worker_translate_s_max": cstats.get("worker_translate_s_max"),
+                    "worker_nvrtc_link_s_max": cstats.get("worker_nvrtc_link_s_max"),
+                    "cached_s": t_cached, "bind_s": t_link, "modules_in_batch": rb.n_modules, "pool_workers": pool_info["workers"],
                     "pool_warmup_s_max": pool_info["warmup_s_max"], "evaluator_and_pool_ready_s": t_pool,
                     "population_generation_s": t_gen, "host_cores": host_cores(),
                     "note": "cold population, worker processes; not part of a step (e2e_fresh is the number that includes it)"},
@@ -487,6 +490,7 @@ def main():
     ap.add_argument("--fresh-steps", type=int, default=2, help="timed fresh generations for e2e_fresh (0 = skip)")
     ap.add_argument("--teams", type=int, default=0, help="warps (episodes) per CTA; 0 = planner's choice")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--single-module", action="store_true", help="relink the batch's structures into one module (one launch)")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

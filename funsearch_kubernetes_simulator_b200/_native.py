@@ -91,6 +91,8 @@ _SIGNATURES = {
     "ks_program_link": (C.c_int, [C.c_int, C.POINTER(C.c_longlong), C.POINTER(C.c_longlong)]),
     "ks_program_link_check": (C.c_int, [C.c_int, C.POINTER(C.c_longlong), C.POINTER(C.c_longlong)]),
     "ks_program_release": (C.c_int, [C.c_longlong]),
+    "ks_program_link_image": (C.c_int, [C.c_int, C.POINTER(C.c_longlong), C.c_char_p]),
+    "ks_program_load_image": (C.c_int, [C.c_void_p, C.c_longlong, C.c_int, C.POINTER(C.c_longlong), C.POINTER(C.c_longlong)]),
     "ks_plan": (C.c_int, [C.POINTER(KsPlan)]),
     "ks_eval_batch": (C.c_int, [C.c_longlong, C.POINTER(KsPlan), C.POINTER(KsBatch), C.c_void_p]),
     "ks_eval_batch_static": (C.c_int, [C.c_longlong, C.POINTER(KsPlan), C.POINTER(KsBatch), C.c_void_p]),

@@ -6,10 +6,12 @@ A generation goes through the pool in two phases:
 
   1. translate: the fresh SOURCES are cut into one slice per worker; each worker returns, per source, the
      structure it translates to (CUDA text, symbol, flags) and the policy's float literals;
-  2. nvrtc: the parent keeps one copy of every structure it has not compiled yet -- a generation of 1,024
-     mutated sources is typically a few hundred structures, often far fewer -- forms groups of
-     `batch` structures (one NVRTC program each) and deals the groups to the workers, which leave the cubins in
-     the shared cache directory (ks_set_cache_dir); the parent then registers the same groups, which are cache hits.
+  2. nvrtc + link: the parent keeps one copy of every structure it has not compiled yet -- a generation of 1,024
+     mutated sources is a few hundred structures, often far fewer -- forms groups of `batch` structures (one NVRTC
+     program each) and deals the groups to the workers, which leave the cubins in the shared cache directory
+     (ks_set_cache_dir) and link what they compiled with the replay kernel into one loadable module per worker
+     (nvJitLink serialises inside a process, so linking in the workers is what makes it parallel); the parent then
+     registers the same groups, which are cache hits, and loads the modules.
 
 No CUDA context is touched in the workers.  They are started when the evaluator is constructed (start()), not
 inside the first evaluation, and warm themselves up (imports, mapping libnvrtc and its builtins, one trivial
@@ -84,6 +86,22 @@ def compile_group(lib, group: Sequence[Structure]) -> Tuple[List[int], List[int]
     return [int(status[i]) for i in range(n)], [int(handles[i]) for i in range(n)]
 
 
+def _nvrtc_link(lib, groups, image_path: str) -> dict:
+    """Compile `groups` (one NVRTC program each, cubins left in the shared cache) and link all of their structures, in
+    order, with the replay kernel into a loadable module written to `image_path` (ks_program_link_image; no GPU is
+    touched).  The parent registers the same groups and loads the image (ks_program_load_image)."""
+    status, handles = [], []
+    for g in groups:
+        st, hs = compile_group(lib, g)
+        status.append(st)
+        handles.extend(hs)
+    linked = False
+    if all(x == 0 for st in status for x in st):
+        arr = (C.c_longlong * len(handles))(*handles)
+        linked = lib.ks_program_link_image(len(handles), arr, image_path.encode()) == 0
+    return {"status": status, "linked": linked}
+
+
 def _send(pipe, obj) -> None:
     data = pickle.dumps(obj, protocol=pickle.HIGHEST_PROTOCOL)
     pipe.write(struct.pack("<Q", len(data)))
@@ -125,6 +143,8 @@ def _worker_main(cache_dir: str, batch: int) -> None:
                 res = _translate_slice(payload)
             elif kind == "nvrtc":
                 res = [compile_group(lib, g)[0] for g in payload]
+            elif kind == "nvrtc_link":
+                res = _nvrtc_link(lib, *payload)
             else:
                 raise ValueError(kind)
             _send(out, ("ok", res, time.perf_counter() - t0))

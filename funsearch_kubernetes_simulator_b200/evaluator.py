@@ -70,32 +70,43 @@ class EpisodeOutcome:
         return placed[key]
 
 
-def table_order(ep_policy: np.ndarray, ep_const: Optional[np.ndarray] = None) -> Optional[np.ndarray]:
-    """Stable permutation that makes the episode table structure-major (and policy-major inside a structure), or None
-    when it already is.  The kernel hands each CTA a contiguous range of the table, so episodes that run the same
-    device function sit side by side on one SM and share its code in the instruction cache
+def table_order(*keys: np.ndarray) -> Optional[np.ndarray]:
+    """Stable permutation that sorts the episode table by `keys` (most significant first: module, structure slot,
+    policy), or None when it already is sorted.  The kernel hands each CTA a contiguous range of the table, so episodes
+    that run the same device function sit side by side on one SM and share its code in the instruction cache
     (csrc/ks_sim_kernel.cu, work distribution)."""
-    ep_policy = np.asarray(ep_policy)
-    if ep_policy.size < 2:
+    n = len(keys[0])
+    if n < 2:
         return None
-    if ep_const is None:
-        if np.all(ep_policy[1:] >= ep_policy[:-1]):
-            return None
-        return np.argsort(ep_policy, kind="stable")
-    key = ep_policy.astype(np.int64) * (1 << 32) + np.asarray(ep_const).astype(np.int64)
-    if np.all(key[1:] >= key[:-1]):
+    order = np.lexsort(tuple(np.asarray(k) for k in reversed(keys)))   # lexsort: last key is the primary one
+    if np.array_equal(order, np.arange(n)):
         return None
-    return np.argsort(key, kind="stable")
+    return order
+
+
+@dataclass
+class Module:
+    """One linked and loaded program: the replay kernel + a set of policy structures."""
+    program: int
+    slot_of: dict            # structure handle -> slot in the module's dispatch table
+    last_use: int = 0
 
 
 @dataclass
 class BoundPolicies:
-    """A list of compiled policies bound to a linked program: the table slot (structure) and the start of the float
-    literals of each, plus the literals of all of them back to back."""
-    program: int
+    """A list of compiled policies bound to loaded modules: per policy the module, the table slot (structure) and the
+    start of its float literals; the literals of all of them back to back."""
+    modules: List[Module]
+    part: np.ndarray        # int32 [n_policies]: index into `modules`
     slot: np.ndarray        # int32 [n_policies]
     const_off: np.ndarray   # int32 [n_policies]
     consts: np.ndarray      # float64
+
+    @property
+    def program(self) -> int:
+        if len(self.modules) != 1:
+            raise ValueError("policies are spread over several modules")
+        return self.modules[0].program
 
 
 @dataclass
@@ -111,6 +122,13 @@ class PopulationReport:
 
 class BatchEvaluator:
     """Traces + one cluster resident on one GPU; evaluates batches of episodes."""
+
+    COMPILE_BATCH = 16          # structures per NVRTC program (ks_set_compile_batch)
+    POOL_SOURCES = 48           # fresh sources from which translating in the pool pays off
+    POOL_STRUCTURES = 24        # new structures from which NVRTC + link in the pool pays off
+    MAX_MODULES = 64            # loaded modules kept (least recently used ones are released)
+    MAX_PARTS = 20              # modules one batch may be spread over before its structures are relinked into one
+    SINGLE_MODULE_WAVES = 8     # batches this many waves long are relinked into one module (one tail instead of many)
 
     def __init__(self, cluster: ClusterSpec, traces: Sequence[Trace], device: int = 0,
                  snapshot_interval: float = 0.05, cache_dir: Optional[str] = None, processes: Optional[int] = None):
@@ -140,9 +158,12 @@ class BatchEvaluator:
             table[i] = (d_pod.data_ptr(), d_heap.data_ptr(), d_place.data_ptr(), tr.n_pods)
         self._trace_table = torch.from_numpy(table).to(self.device)
         self.max_pods = max([t.n_pods for t in self.traces] + [1])
-        self._programs: List[Tuple[frozenset, dict, int]] = []   # (structure handles, handle -> slot, program), newest last
+        self._modules: List[Module] = []
+        self._module_of: dict = {}     # structure handle -> newest module holding it
         self._pinned: set = set()
-        self._scratch: dict = {}   # per stream
+        self._clock = 0
+        self._streams: list = []
+        self._errors: dict = {}
         self.last_plan = None
         self.last_kernel_ms = None
         self.last_compile_stats: dict = {}
@@ -150,6 +171,7 @@ class BatchEvaluator:
         self.sm_count = torch.cuda.get_device_properties(self.device).multi_processor_count
         self.warps_per_team = 0   # 0 = planner's choice; set to force a team width
         self.ctas_per_sm = 0      # 0 = planner's choice; 1 = latency kernel, 2 = dense (throughput) kernel
+        self.module_structures = 0  # test knob: at most this many structures per linked module (0 = no limit)
         # Compile workers are started now, not inside the first evaluation: they warm up (imports, libnvrtc) while the
         # caller is still generating its first population.
         if processes is None:
@@ -169,26 +191,22 @@ class BatchEvaluator:
         nat.check(self.lib.ks_set_compile_batch(self.COMPILE_BATCH))
 
     # ------------------------------------------------------------------ policies
-    COMPILE_BATCH = 16          # structures per NVRTC program (ks_set_compile_batch)
-    POOL_SOURCES = 48           # fresh sources from which translating in the pool pays off
-    POOL_STRUCTURES = 24        # new structures from which NVRTC in the pool pays off
-    MAX_PROGRAMS = 12           # linked modules kept loaded (least recently used ones are released)
-
     def compile(self, sources: Sequence[str], threads: int = 0, processes: Optional[int] = None) -> List[Optional[CompiledPolicy]]:
         """Python policy sources -> compiled policies (structure function + float literals).
         A source outside the supported subset yields None (its episodes are reported as not evaluated).
         A generation of fresh sources is translated by the pool of worker processes started with the evaluator
         (`processes=0` keeps everything in this process); only structures never seen before reach NVRTC, in groups
-        of COMPILE_BATCH, again on the pool."""
+        of COMPILE_BATCH, again on the pool, and each worker also links what it compiled with the replay kernel:
+        this process only loads the finished modules."""
         import time
         from . import compile_pool, policy_compiler
-        stats = {"sources": len(sources), "fresh_sources": 0, "new_structures": 0, "translate_s": 0.0, "nvrtc_s": 0.0,
-                 "register_s": 0.0, "pool_workers": 0, "worker_translate_s_max": 0.0, "worker_nvrtc_s_max": 0.0}
+        stats = {"sources": len(sources), "fresh_sources": 0, "new_structures": 0, "translate_s": 0.0, "nvrtc_link_s": 0.0,
+                 "register_load_s": 0.0, "pool_workers": 0, "worker_translate_s_max": 0.0, "worker_nvrtc_link_s_max": 0.0,
+                 "modules_loaded": 0}
         use_pool = (self.processes if processes is None else processes) > 1 and compile_pool.n_workers() > 0
         t0 = time.perf_counter()
-        fresh = [s for s in dict.fromkeys(sources) if policy_compiler.cached(s) is None]
+        fresh = [s for s in dict.fromkeys(sources) if policy_compiler.cached(s) is None and s not in self._errors]
         stats["fresh_sources"] = len(fresh)
-        self._errors = getattr(self, "_errors", {})
         if use_pool and len(fresh) >= self.POOL_SOURCES:
             nw = compile_pool.n_workers()
             per = -(-len(fresh) // nw)
@@ -230,18 +248,33 @@ class BatchEvaluator:
                 if len(groups) < nw:   # fewer programs than workers: smaller programs, all workers busy
                     g = max(4, -(-len(structs) // nw))
                     groups = [structs[i:i + g] for i in range(0, len(structs), g)]
-                jobs = [groups[i::nw] for i in range(nw) if groups[i::nw]]
-                _res, secs = compile_pool.run_jobs("nvrtc", jobs)
+                per_worker = [groups[i::nw] for i in range(nw) if groups[i::nw]]
+                images = [os.path.join(compile_pool.cache_dir(), f"module_{os.getpid()}_{self._clock}_{k}.cubin")
+                          for k in range(len(per_worker))]
+                self._clock += 1
+                res, secs = compile_pool.run_jobs("nvrtc_link", [(gs, img) for gs, img in zip(per_worker, images)])
                 stats["pool_workers"] = compile_pool.n_workers()
-                stats["worker_nvrtc_s_max"] = max(secs) if secs else 0.0
-                stats["nvrtc_s"] = time.perf_counter() - t0
+                stats["worker_nvrtc_link_s_max"] = max(secs) if secs else 0.0
+                stats["nvrtc_link_s"] = time.perf_counter() - t0
                 t0 = time.perf_counter()
                 self._register_groups(groups, 1)   # cubins are in the shared cache: these are hits
+                for gs, img, r in zip(per_worker, images, res):
+                    if r is None or not r.get("linked") or not os.path.exists(img):
+                        continue   # bind() links whatever has no module yet
+                    handles = [policy_compiler._STRUCT_HANDLES[sym] for g in gs for (_src, sym, _fl) in g]
+                    with open(img, "rb") as f:
+                        blob = f.read()
+                    os.unlink(img)
+                    arr = (C.c_longlong * len(handles))(*handles)
+                    prog = C.c_longlong(-1)
+                    nat.check(self.lib.ks_program_load_image(blob, len(blob), len(handles), arr, C.byref(prog)))
+                    self._add_module(Module(prog.value, {h: i for i, h in enumerate(handles)}))
+                    stats["modules_loaded"] += 1
             else:
                 self._register_groups(groups, threads)
-                stats["nvrtc_s"] = time.perf_counter() - t0
+                stats["nvrtc_link_s"] = time.perf_counter() - t0
                 t0 = time.perf_counter()
-        stats["register_s"] = time.perf_counter() - t0
+        stats["register_load_s"] = time.perf_counter() - t0
         self.last_compile_stats = stats
         return out
 
@@ -268,46 +301,78 @@ class BatchEvaluator:
 
     def compile_error(self, source: str) -> Optional[str]:
         """Why `source` was declined by the translator (None if it was not)."""
-        return getattr(self, "_errors", {}).get(source)
+        return self._errors.get(source)
 
-    def bind(self, policies: Sequence[CompiledPolicy], pin: bool = False) -> BoundPolicies:
-        """Link (or find) a program that holds the structures of `policies` and lay out their float literals."""
+    # ------------------------------------------------------------------ modules
+    def _add_module(self, m: Module) -> Module:
+        self._clock += 1
+        m.last_use = self._clock
+        self._modules.append(m)
+        for h in m.slot_of:
+            self._module_of[h] = m
+        while len(self._modules) > self.MAX_MODULES:
+            victims = [x for x in self._modules if x.program not in self._pinned and x is not m]
+            if not victims:
+                break
+            old = min(victims, key=lambda x: x.last_use)
+            self._modules.remove(old)
+            for h in list(old.slot_of):
+                if self._module_of.get(h) is old:
+                    del self._module_of[h]
+                    for other in self._modules:      # another module may still hold the structure
+                        if h in other.slot_of:
+                            self._module_of[h] = other
+                            break
+            self.lib.ks_program_release(old.program)
+        return m
+
+    def _link_module(self, handles: Sequence[int]) -> Module:
+        order = sorted(set(handles))
+        arr = (C.c_longlong * len(order))(*order)
+        out = C.c_longlong(-1)
+        nat.check(self.lib.ks_program_link(len(order), arr, C.byref(out)))
+        return self._add_module(Module(out.value, {h: i for i, h in enumerate(order)}))
+
+    def bind(self, policies: Sequence[CompiledPolicy], pin: bool = False, single_module: bool = False) -> BoundPolicies:
+        """Find (or link) modules that hold the structures of `policies` and lay out their float literals.  Structures
+        keep the module they were first linked into, so a generation that mostly re-tunes constants, or repeats last
+        generation's elites, links only what is new; a batch spread over more than MAX_PARTS modules (or asked to be
+        in one) has its structures relinked into a single module."""
         handles = []
         for p in policies:
             if p.handle is None:
                 raise ValueError("policy was not compiled by BatchEvaluator.compile")
             handles.append(int(p.handle))
-        need = frozenset(handles)
-        hit = None
-        for k in range(len(self._programs) - 1, -1, -1):
-            if need <= self._programs[k][0]:
-                hit = self._programs.pop(k)
-                break
-        if hit is None:
-            order = sorted(need)
-            if len(order) > nat.KS_MAX_TABLE:
-                raise ValueError(f"{len(order)} distinct policy structures in one batch; a program holds {nat.KS_MAX_TABLE}")
-            arr = (C.c_longlong * len(order))(*order)
-            out = C.c_longlong(-1)
-            nat.check(self.lib.ks_program_link(len(order), arr, C.byref(out)))
-            hit = (need, {h: i for i, h in enumerate(order)}, out.value)
-        self._programs.append(hit)   # most recently used last
-        if pin:
-            self._pinned.add(hit[2])
-        while len(self._programs) > self.MAX_PROGRAMS:
-            victims = [k for k, pr in enumerate(self._programs[:-1]) if pr[2] not in self._pinned]
-            if not victims:
-                break
-            old = self._programs.pop(victims[0])
-            self.lib.ks_program_release(old[2])
-        slot_of = hit[1]
-        slot = np.array([slot_of[h] for h in handles], dtype=np.int32)
+        need = sorted(set(handles))
+        missing = [h for h in need if h not in self._module_of]
+        cap = min(nat.KS_MAX_TABLE, self.module_structures or nat.KS_MAX_TABLE)
+        for i in range(0, len(missing), cap):
+            self._link_module(missing[i:i + cap])
+        used = {id(self._module_of[h]) for h in need}
+        if (len(used) > self.MAX_PARTS or (single_module and len(used) > 1)) and not self.module_structures:
+            for i in range(0, len(need), nat.KS_MAX_TABLE):
+                self._link_module(need[i:i + nat.KS_MAX_TABLE])   # newest module wins in _module_of
+        mods: List[Module] = []
+        index = {}
+        self._clock += 1
+        part = np.zeros(len(handles), dtype=np.int32)
+        slot = np.zeros(len(handles), dtype=np.int32)
+        for k, h in enumerate(handles):
+            m = self._module_of[h]
+            if id(m) not in index:
+                index[id(m)] = len(mods)
+                mods.append(m)
+                m.last_use = self._clock
+                if pin:
+                    self._pinned.add(m.program)
+            part[k] = index[id(m)]
+            slot[k] = m.slot_of[h]
         lens = np.array([len(p.consts) for p in policies], dtype=np.int64)
         off = np.concatenate([[0], np.cumsum(lens)[:-1]]) if len(policies) else np.zeros(0, np.int64)
         if lens.sum() >= 2 ** 31:
             raise ValueError("too many float literals in one batch")
         consts = np.array([c for p in policies for c in p.consts] or [0.0], dtype=np.float64)
-        return BoundPolicies(hit[2], slot, off.astype(np.int32), consts)
+        return BoundPolicies(mods, part, slot, off.astype(np.int32), consts)
 
     def _program(self, handles: Tuple[int, ...]) -> int:
         """Program holding exactly these structure handles, slot i = handles[i] (test hooks)."""
@@ -317,19 +382,25 @@ class BatchEvaluator:
         self._pinned.add(out.value)
         return out.value
 
+    def _side_streams(self, n: int):
+        torch = self._torch
+        while len(self._streams) < n:
+            self._streams.append(torch.cuda.Stream(device=self.device))
+        return self._streams[:n]
+
     # ------------------------------------------------------------------ evaluation
     def plan(self, n_episodes: int, want_placements: bool, max_pods: Optional[int] = None,
              teams_per_block: int = 0, warps_per_team: int = 0,
-             episodes_per_policy: float = 1.0) -> nat.KsPlan:
+             episodes_per_policy: float = 1.0, allow_dense: bool = True) -> nat.KsPlan:
         """Launch geometry (ks_plan).  The two-CTAs-per-SM kernel is chosen for batches of several waves whose table
-        holds runs of same-policy episodes (policy-major order): warps of one SM then share a policy's code in the
-        instruction cache and the extra resident warps hide latency; with a different policy per warp they thrash it
+        holds runs of same-structure episodes: warps of one SM then share a policy's code in the
+        instruction cache and the extra resident warps hide latency; with a different function per warp they thrash it
         (measured: +23 % on 512 policies x 16 traces, -6 % on 4,096 policies x 1 trace)."""
         p = nat.KsPlan()
         p.warps_per_team = warps_per_team or self.warps_per_team
         p.ctas_per_sm = self.ctas_per_sm
         if p.ctas_per_sm == 0 and p.warps_per_team <= 1 and self.cluster.n_nodes <= 64 and teams_per_block == 0 \
-                and episodes_per_policy >= 8 and n_episodes >= 2 * 16 * self.sm_count:
+                and allow_dense and episodes_per_policy >= 8 and n_episodes >= 2 * 16 * self.sm_count:
             p.ctas_per_sm = 2
         p.n_episodes = n_episodes
         p.n_nodes = self.cluster.n_nodes
@@ -342,72 +413,26 @@ class BatchEvaluator:
     def run_episodes(self, policies: Sequence[CompiledPolicy], ep_policy: Sequence[int], ep_trace: Sequence[int],
                      want_placements: bool = False, max_events: int = 0, teams_per_block: int = 0,
                      stream=None) -> List[EpisodeOutcome]:
-        """Evaluate episodes e = (policies[ep_policy[e]], traces[ep_trace[e]]) in one kernel launch."""
-        torch = self._torch
-        n_ep = len(ep_policy)
-        if n_ep == 0:
+        """Evaluate episodes e = (policies[ep_policy[e]], traces[ep_trace[e]]): one kernel launch per module the
+        policies' structures live in (one launch when they share a module), all in flight together."""
+        if len(ep_policy) == 0:
             return []
-        ep_policy = np.ascontiguousarray(ep_policy, dtype=np.int64)
-        ep_trace = np.ascontiguousarray(ep_trace, dtype=np.int32)
-        if ep_policy.min() < 0 or ep_policy.max() >= len(policies) or ep_trace.min() < 0 or ep_trace.max() >= len(self.traces):
-            raise ValueError("episode table refers to an unknown policy or trace")
-        bound = self.bind(policies)
-        ep_slot = np.ascontiguousarray(bound.slot[ep_policy])
-        ep_const = np.ascontiguousarray(bound.const_off[ep_policy])
-        order = table_order(ep_slot, ep_const)
-        if order is not None:
-            ep_slot, ep_const, ep_trace = (np.ascontiguousarray(a[order]) for a in (ep_slot, ep_const, ep_trace))
-        pods_per_ep = np.array([self.traces[t].n_pods for t in ep_trace], dtype=np.int64)
-        plan = self.plan(n_ep, want_placements, int(pods_per_ep.max()), teams_per_block,
-                         episodes_per_policy=n_ep / len(np.unique(ep_slot)))
-        self.last_plan = plan
+        rb = ResidentBatch(self, policies, ep_policy, ep_trace, teams_per_block, want_placements=want_placements,
+                           max_events=max_events, pin=False)
+        self.last_plan = rb.plans[0]
+        torch = self._torch
         st = stream or torch.cuda.current_stream(self.device)
-        # copies, launch and read-back are all ordered on `st`
-        with torch.cuda.device(self.device), torch.cuda.stream(st):
-            d_pol = torch.from_numpy(ep_slot).to(self.device, non_blocking=True)
-            d_cof = torch.from_numpy(ep_const).to(self.device, non_blocking=True)
-            d_kf = torch.from_numpy(bound.consts).to(self.device, non_blocking=True)
-            d_tr = torch.from_numpy(ep_trace).to(self.device, non_blocking=True)
-            d_res = torch.empty(n_ep * nat.RESULT_DTYPE.itemsize, dtype=torch.uint8, device=self.device)
-            # one scratch buffer per stream: calls on different streams may overlap on the GPU
-            key = int(st.cuda_stream)
-            scratch = self._scratch.get(key)
-            if scratch is None or scratch.numel() < plan.scratch_bytes:
-                scratch = self._scratch[key] = torch.empty(int(plan.scratch_bytes), dtype=torch.uint8, device=self.device)
-            d_place = d_off = None
-            if want_placements:
-                padded = (pods_per_ep + 1) // 2 * 2
-                off = np.concatenate([[0], np.cumsum(padded)[:-1]]).astype(np.int64)
-                d_off = torch.from_numpy(off).to(self.device, non_blocking=True)
-                d_place = torch.empty(int(padded.sum()), dtype=torch.int64, device=self.device)
-            b = nat.KsBatch()
-            b.traces = self._trace_table.data_ptr()
-            b.ep_policy = d_pol.data_ptr()
-            b.ep_const = d_cof.data_ptr()
-            b.consts = d_kf.data_ptr()
-            b.ep_trace = d_tr.data_ptr()
-            b.nconst = self._nconst.data_ptr()
-            b.results = d_res.data_ptr()
-            b.placements = d_place.data_ptr() if want_placements else None
-            b.place_off = d_off.data_ptr() if want_placements else None
-            b.scratch = scratch.data_ptr()
-            for k in range(4):
-                b.totals[k] = int(self._totals[k])
-            b.max_events = max_events
-            b.snapshot_interval = self.snapshot_interval
+        with torch.cuda.device(self.device):
             e0 = torch.cuda.Event(enable_timing=True)
             e1 = torch.cuda.Event(enable_timing=True)
             e0.record(st)
-            nat.check(self.lib.ks_eval_batch(bound.program, C.byref(plan), C.byref(b), C.c_void_p(st.cuda_stream)))
+            rb.launch(st)
             e1.record(st)
-            h_res = d_res.to("cpu", non_blocking=True)
-            h_place = d_place.to("cpu", non_blocking=True) if want_placements else None
-            st.synchronize()
-            res = np.frombuffer(h_res.numpy().tobytes(), dtype=nat.RESULT_DTYPE)
+            res = rb.results(st)
             self.last_kernel_ms = e0.elapsed_time(e1)
-            place = h_place.numpy().view(np.uint64) if want_placements else None
+            place = rb.placements(st) if want_placements else None
         out = []
-        for e in range(n_ep):
+        for e in range(rb.n_ep):
             r = res[e]
             results = None
             if r["num_snapshots"] > 0:
@@ -419,20 +444,15 @@ class BatchEvaluator:
                                 int(r["scorer_calls"]), int(r["placed"]), int(r["max_nodes"]), int(r["max_waiting"]),
                                 int(r["last_event_time"]), int(r["device_cycles"]))
             if want_placements:
-                tr = self.traces[ep_trace[e]]
+                tr = self.traces[int(ep_trace[e])]
                 rank = tr.packed()[0]
-                rec = place[off[e]: off[e] + tr.n_pods][rank]   # rank-indexed -> pod_list order
+                rec = place[e][rank]   # rank-indexed -> pod_list order
                 node = ((rec >> np.uint64(8)) & np.uint64(0xFFFF)).astype(np.int64)
                 oc.final_creation_time = (rec >> np.uint64(24)).astype(np.int64)
                 oc.node_index = np.where(node >= nat.KS_NODE_WAITING, -1, node)
                 oc.waiting = node == nat.KS_NODE_WAITING
                 oc.gpu_mask = (rec & np.uint64(0xFF)).astype(np.int64)
             out.append(oc)
-        if order is not None:   # back to the caller's episode order
-            unsorted: List[Optional[EpisodeOutcome]] = [None] * n_ep
-            for k, e in enumerate(order):
-                unsorted[int(e)] = out[k]
-            out = unsorted
         return out
 
     # ------------------------------------------------------------------ test hook: raw scores of (pod, node) cases
@@ -449,22 +469,23 @@ class BatchEvaluator:
         d_out = torch.empty(n, dtype=torch.int64, device=self.device)
         st = torch.cuda.current_stream(self.device)
         kf_ptr = d_kf.data_ptr() + 8 * int(bound.const_off[slot])
-        nat.check(self.lib.ks_debug_score(bound.program, int(bound.slot[slot]), n, C.c_void_p(d_p.data_ptr()), C.c_void_p(d_ns.data_ptr()),
+        prog = bound.modules[int(bound.part[slot])].program
+        nat.check(self.lib.ks_debug_score(prog, int(bound.slot[slot]), n, C.c_void_p(d_p.data_ptr()), C.c_void_p(d_ns.data_ptr()),
                                           C.c_void_p(d_nc.data_ptr()), C.c_void_p(kf_ptr), C.c_void_p(d_out.data_ptr()),
                                           C.c_void_p(st.cuda_stream)))
         return d_out.cpu().numpy()
 
     # ------------------------------------------------------------------ resident form (inputs already in HBM)
     def prepare_resident(self, policies: Sequence[CompiledPolicy], ep_policy: Sequence[int], ep_trace: Sequence[int],
-                         teams_per_block: int = 0) -> "ResidentBatch":
-        return ResidentBatch(self, policies, ep_policy, ep_trace, teams_per_block)
+                         teams_per_block: int = 0, single_module: Optional[bool] = None) -> "ResidentBatch":
+        return ResidentBatch(self, policies, ep_policy, ep_trace, teams_per_block, single_module=single_module)
 
     # ------------------------------------------------------------------ host-buffer (end-to-end) form
     def prepare_host_batch(self, policies: Sequence[CompiledPolicy], ep_policy: Sequence[int], ep_trace: Sequence[int],
-                           teams_per_block: int = 0) -> "HostBatch":
+                           teams_per_block: int = 0, single_module: Optional[bool] = None) -> "HostBatch":
         """Stage a batch in pinned host memory for ks_eval_batch_host (everything the step needs crosses
         PCIe inside the call: traces, cluster table, episode table in; results out)."""
-        return HostBatch(self, policies, ep_policy, ep_trace, teams_per_block)
+        return HostBatch(self, policies, ep_policy, ep_trace, teams_per_block, single_module=single_module)
 
     # ------------------------------------------------------------------ reference-shaped entry points
     def evaluate_population(self, codes: Sequence[str], trace_ids: Optional[Sequence[int]] = None,
@@ -549,70 +570,148 @@ class BatchEvaluator:
             return None
 
 
-def _episode_tables(ev: BatchEvaluator, policies, ep_policy, ep_trace, pin=True):
-    """Bind + structure-major episode table shared by the resident and the host-buffer batch."""
-    ep_policy = np.ascontiguousarray(ep_policy, dtype=np.int64)
-    ep_trace = np.ascontiguousarray(ep_trace, dtype=np.int32)
-    if len(ep_policy) == 0 or ep_policy.min() < 0 or ep_policy.max() >= len(policies) or ep_trace.min() < 0 \
-            or ep_trace.max() >= len(ev.traces):
-        raise ValueError("episode table is empty or refers to an unknown policy or trace")
-    bound = ev.bind(policies, pin=pin)
-    ep_slot = np.ascontiguousarray(bound.slot[ep_policy])
-    ep_const = np.ascontiguousarray(bound.const_off[ep_policy])
-    order = table_order(ep_slot, ep_const)
-    if order is not None:
-        ep_slot, ep_const, ep_trace = (np.ascontiguousarray(a[order]) for a in (ep_slot, ep_const, ep_trace))
-    return bound, ep_slot, ep_const, ep_trace, order
+
+class _Tables:
+    """Bind + the episode table sorted module-major, then structure-major, then policy-major; cut into one part per
+    module.  Shared by the resident and the host-buffer batch."""
+
+    def __init__(self, ev: BatchEvaluator, policies, ep_policy, ep_trace, teams_per_block, want_placements, pin,
+                 single_module):
+        ep_policy = np.ascontiguousarray(ep_policy, dtype=np.int64)
+        ep_trace = np.ascontiguousarray(ep_trace, dtype=np.int32)
+        self.n_ep = len(ep_policy)
+        if self.n_ep == 0 or ep_policy.min() < 0 or ep_policy.max() >= len(policies) or ep_trace.min() < 0 \
+                or ep_trace.max() >= len(ev.traces):
+            raise ValueError("episode table is empty or refers to an unknown policy or trace")
+        if single_module is None:   # long batches: one module, one tail (the relink is small next to the run)
+            single_module = self.n_ep >= ev.SINGLE_MODULE_WAVES * 8 * ev.sm_count
+        self.bound = bound = ev.bind(policies, pin=pin, single_module=single_module)
+        part = bound.part[ep_policy]
+        self.ep_slot = bound.slot[ep_policy]
+        self.ep_const = bound.const_off[ep_policy]
+        self.ep_trace = ep_trace
+        self.order = table_order(part, self.ep_slot, self.ep_const)
+        if self.order is not None:
+            part = part[self.order]
+            self.ep_slot, self.ep_const, self.ep_trace = (np.ascontiguousarray(a[self.order])
+                                                          for a in (self.ep_slot, self.ep_const, self.ep_trace))
+            self.inverse = np.argsort(self.order)
+        else:
+            self.ep_slot, self.ep_const = np.ascontiguousarray(self.ep_slot), np.ascontiguousarray(self.ep_const)
+        self.n_structures = int(len(np.unique(part.astype(np.int64) * nat.KS_MAX_TABLE + self.ep_slot)))
+        self.pods_per_ep = np.array([ev.traces[t].n_pods for t in self.ep_trace], dtype=np.int64)
+        # one part per module: [start, end) of the sorted table
+        cuts = [0] + [int(i) for i in np.nonzero(np.diff(part))[0] + 1] + [self.n_ep]
+        self.parts = [(bound.modules[int(part[a])], a, b) for a, b in zip(cuts[:-1], cuts[1:])]
+        # geometry: the same number of episodes per CTA in every part, chosen so that all CTAs are resident together
+        n_parts = len(self.parts)
+        dense_ok = n_parts == 1
+        tpb = teams_per_block
+        if n_parts > 1 and tpb == 0:
+            w = ev.warps_per_team or ev.plan(1, False, 1).warps_per_team
+            lim = max(1, (16 if w > 8 else 8) // max(1, w))
+            tpb = max(1, min(lim, -(-self.n_ep // ev.sm_count)))
+            while tpb < lim and sum(-(-(b - a) // tpb) for _m, a, b in self.parts) > ev.sm_count:
+                tpb += 1
+        self.plans = []
+        for _m, a, b in self.parts:
+            self.plans.append(ev.plan(b - a, want_placements, int(self.pods_per_ep[a:b].max()), tpb,
+                                      episodes_per_policy=self.n_ep / self.n_structures, allow_dense=dense_ok))
 
 
 class ResidentBatch:
-    """A batch whose episode table, result buffer and scratch already live in HBM: launch() is exactly one
-    ks_eval_batch call (one memset + one kernel), nothing else."""
+    """A batch whose episode table, result buffer and scratch already live in HBM: launch() is one ks_eval_batch call
+    (one memset + one kernel) per module the batch's structures live in, all in flight together, nothing else."""
 
-    def __init__(self, ev: BatchEvaluator, policies, ep_policy, ep_trace, teams_per_block=0):
+    def __init__(self, ev: BatchEvaluator, policies, ep_policy, ep_trace, teams_per_block=0, want_placements=False,
+                 max_events=0, pin=True, single_module=None):
         torch = ev._torch
         self.ev = ev
-        self.n_ep = len(ep_policy)
-        bound, ep_slot, ep_const, ep_trace, self.order = _episode_tables(ev, policies, ep_policy, ep_trace)
-        self.prog = bound.program
-        self.n_structures = int(len(np.unique(ep_slot)))
-        if self.order is not None:   # the device table is structure-major; results() undoes it
-            self.inverse = np.argsort(self.order)
-            self._d_inverse = torch.from_numpy(self.inverse).to(ev.device)
-        pods_per_ep = [ev.traces[t].n_pods for t in ep_trace]
-        self.plan = ev.plan(self.n_ep, False, max(pods_per_ep), teams_per_block,
-                            episodes_per_policy=self.n_ep / self.n_structures)
-        self.d_pol = torch.from_numpy(ep_slot).to(ev.device)
-        self.d_cof = torch.from_numpy(ep_const).to(ev.device)
-        self.d_kf = torch.from_numpy(bound.consts).to(ev.device)
-        self.d_tr = torch.from_numpy(ep_trace).to(ev.device)
-        self.d_res = torch.zeros(self.n_ep * nat.RESULT_DTYPE.itemsize, dtype=torch.uint8, device=ev.device)
-        self.d_scratch = torch.empty(int(self.plan.scratch_bytes), dtype=torch.uint8, device=ev.device)
-        b = nat.KsBatch()
-        b.traces = ev._trace_table.data_ptr()
-        b.ep_policy = self.d_pol.data_ptr()
-        b.ep_const = self.d_cof.data_ptr()
-        b.consts = self.d_kf.data_ptr()
-        b.ep_trace = self.d_tr.data_ptr()
-        b.nconst = ev._nconst.data_ptr()
-        b.results = self.d_res.data_ptr()
-        b.placements = None
-        b.place_off = None
-        b.scratch = self.d_scratch.data_ptr()
-        for k in range(4):
-            b.totals[k] = int(ev._totals[k])
-        b.max_events = 0
-        b.snapshot_interval = ev.snapshot_interval
-        self.batch = b
+        t = self.tables = _Tables(ev, policies, ep_policy, ep_trace, teams_per_block, want_placements, pin, single_module)
+        self.n_ep = t.n_ep
+        self.order = t.order
+        self.n_structures = t.n_structures
+        self.plans = t.plans
+        self.plan = t.plans[0]
+        self.n_modules = len(t.parts)
+        self.prog = t.parts[0][0].program
+        if t.order is not None:   # the device table is sorted; results() undoes it
+            self.inverse = t.inverse
+            self._d_inverse = torch.from_numpy(t.inverse).to(ev.device)
+        rec = nat.RESULT_DTYPE.itemsize
+        with torch.cuda.device(ev.device):
+            self.d_pol = torch.from_numpy(t.ep_slot).to(ev.device)
+            self.d_cof = torch.from_numpy(t.ep_const).to(ev.device)
+            self.d_kf = torch.from_numpy(t.bound.consts).to(ev.device)
+            self.d_tr = torch.from_numpy(t.ep_trace).to(ev.device)
+            self.d_res = torch.zeros(self.n_ep * rec, dtype=torch.uint8, device=ev.device)
+            self.d_place = self.d_off = None
+            if want_placements:
+                padded = (t.pods_per_ep + 1) // 2 * 2
+                self.place_off = np.concatenate([[0], np.cumsum(padded)[:-1]]).astype(np.int64)
+                self.d_off = torch.from_numpy(self.place_off).to(ev.device)
+                self.d_place = torch.empty(int(padded.sum()), dtype=torch.int64, device=ev.device)
+            self.d_scratch = [torch.empty(int(p.scratch_bytes), dtype=torch.uint8, device=ev.device) for p in self.plans]
+        self.batches = []
+        for (m, a, b), plan, scratch in zip(t.parts, self.plans, self.d_scratch):
+            kb = nat.KsBatch()
+            kb.traces = ev._trace_table.data_ptr()
+            kb.ep_policy = self.d_pol.data_ptr() + 4 * a
+            kb.ep_const = self.d_cof.data_ptr() + 4 * a
+            kb.consts = self.d_kf.data_ptr()
+            kb.ep_trace = self.d_tr.data_ptr() + 4 * a
+            kb.nconst = ev._nconst.data_ptr()
+            kb.results = self.d_res.data_ptr() + rec * a
+            kb.placements = self.d_place.data_ptr() if want_placements else None
+            kb.place_off = self.d_off.data_ptr() + 8 * a if want_placements else None
+            kb.scratch = scratch.data_ptr()
+            for k in range(4):
+                kb.totals[k] = int(ev._totals[k])
+            kb.max_events = max_events
+            kb.snapshot_interval = ev.snapshot_interval
+            self.batches.append((m.program, plan, kb))
+        self.batch = self.batches[0][2]
+        self._fork = torch.cuda.Event()
+        self._joins = [torch.cuda.Event() for _ in self.batches]
 
     def launch(self, stream=None) -> None:
+        """Enqueue the batch on `stream` (default: torch's current stream).  With several modules the launches go to
+        side streams that fork from and join back into `stream`, so they run concurrently and `stream` order holds."""
         torch = self.ev._torch
         st = stream or torch.cuda.current_stream(self.ev.device)
-        nat.check(self.ev.lib.ks_eval_batch(self.prog, C.byref(self.plan), C.byref(self.batch), C.c_void_p(st.cuda_stream)))
+        lib = self.ev.lib
+        if len(self.batches) == 1:
+            prog, plan, kb = self.batches[0]
+            nat.check(lib.ks_eval_batch(prog, C.byref(plan), C.byref(kb), C.c_void_p(st.cuda_stream)))
+            return
+        side = self.ev._side_streams(len(self.batches))
+        self._fork.record(st)
+        for (prog, plan, kb), s, j in zip(self.batches, side, self._joins):
+            s.wait_event(self._fork)
+            nat.check(lib.ks_eval_batch(prog, C.byref(plan), C.byref(kb), C.c_void_p(s.cuda_stream)))
+            j.record(s)
+        for j in self._joins:
+            st.wait_event(j)
 
-    def results(self) -> np.ndarray:
-        res = np.frombuffer(self.d_res.cpu().numpy().tobytes(), dtype=nat.RESULT_DTYPE)
+    def _to_host(self, dev_tensor, stream):
+        torch = self.ev._torch
+        st = stream or torch.cuda.current_stream(self.ev.device)
+        with torch.cuda.stream(st):
+            h = dev_tensor.to("cpu", non_blocking=True)
+        st.synchronize()
+        return h
+
+    def results(self, stream=None) -> np.ndarray:
+        """KsResult records in the caller's episode order (waits for `stream`)."""
+        res = np.frombuffer(self._to_host(self.d_res, stream).numpy().tobytes(), dtype=nat.RESULT_DTYPE)
         return res if self.order is None else res[self.inverse]
+
+    def placements(self, stream=None) -> list:
+        """Per episode (caller's order): the rank-indexed placement records."""
+        place = self._to_host(self.d_place, stream).numpy().view(np.uint64)
+        t = self.tables
+        rows = [place[self.place_off[k]: self.place_off[k] + t.pods_per_ep[k]] for k in range(self.n_ep)]
+        return rows if self.order is None else [rows[int(self.inverse[e])] for e in range(self.n_ep)]
 
     def scores_tensor(self):
         """Per-episode policy_score as a device fp64 tensor (a strided view of the result records)."""
@@ -623,31 +722,31 @@ class ResidentBatch:
 
 
 class HostBatch:
-    """One batch held in pinned host memory + a device workspace; run() = one ks_eval_batch_host call."""
+    """One batch held in pinned host memory + device workspaces; run() = one ks_eval_batch_host call per module the
+    batch's structures live in (concurrently, each on its own stream)."""
 
-    def __init__(self, ev: BatchEvaluator, policies, ep_policy, ep_trace, teams_per_block=0):
+    def __init__(self, ev: BatchEvaluator, policies, ep_policy, ep_trace, teams_per_block=0, single_module=None):
         torch = ev._torch
         self.ev = ev
-        self.n_ep = len(ep_policy)
-        bound, ep_slot, ep_const, ep_trace, self.order = _episode_tables(ev, policies, ep_policy, ep_trace)
-        self.prog = bound.program
-        if self.order is not None:   # the table that crosses PCIe is structure-major; run() undoes it
-            self.inverse = np.argsort(self.order)
-        pods_per_ep = [ev.traces[t].n_pods for t in ep_trace]
-        self.plan = ev.plan(self.n_ep, False, max(pods_per_ep), teams_per_block,
-                            episodes_per_policy=self.n_ep / len(np.unique(ep_slot)))
+        t = self.tables = _Tables(ev, policies, ep_policy, ep_trace, teams_per_block, False, True, single_module)
+        self.n_ep = t.n_ep
+        self.order = t.order
+        if t.order is not None:   # the table that crosses PCIe is sorted; run() undoes it
+            self.inverse = t.inverse
+        self.plans = t.plans
+        self.plan = t.plans[0]
+        rec = nat.RESULT_DTYPE.itemsize
 
         def pinned(a: np.ndarray):
-            t = torch.from_numpy(np.ascontiguousarray(a)).pin_memory()
-            return t
+            return torch.from_numpy(np.ascontiguousarray(a)).pin_memory()
         self._keep = []
         nconst, totals = ev.cluster.packed()
         self.h_nconst = pinned(nconst)
-        self.h_pol = pinned(ep_slot)
-        self.h_cof = pinned(ep_const)
-        self.h_kf = pinned(bound.consts)
-        self.h_tr = pinned(ep_trace)
-        self.h_res = torch.empty(self.n_ep * nat.RESULT_DTYPE.itemsize, dtype=torch.uint8).pin_memory()
+        self.h_pol = pinned(t.ep_slot)
+        self.h_cof = pinned(t.ep_const)
+        self.h_kf = pinned(t.bound.consts)
+        self.h_tr = pinned(t.ep_trace)
+        self.h_res = torch.empty(self.n_ep * rec, dtype=torch.uint8).pin_memory()
         self.h_traces = (nat.KsHostTrace * len(ev.traces))()
         for i, tr in enumerate(ev.traces):
             _r, podrec, heap0, place0 = tr.packed()
@@ -657,39 +756,60 @@ class HostBatch:
             self.h_traces[i].heap0 = bufs[1].data_ptr()
             self.h_traces[i].place0 = bufs[2].data_ptr()
             self.h_traces[i].n_pods = tr.n_pods
-        hb = nat.KsHostBatch()
-        hb.traces = self.h_traces
-        hb.n_traces = len(ev.traces)
-        hb.ep_policy = self.h_pol.data_ptr()
-        hb.ep_const = self.h_cof.data_ptr()
-        hb.consts = self.h_kf.data_ptr()
-        hb.n_consts = int(bound.consts.size)
-        hb.ep_trace = self.h_tr.data_ptr()
-        hb.nconst = self.h_nconst.data_ptr()
-        hb.results = self.h_res.data_ptr()
-        hb.placements = None
-        hb.place_off = None
-        hb.placements_len = 0
-        for k in range(4):
-            hb.totals[k] = int(totals[k])
-        hb.max_events = 0
-        hb.snapshot_interval = ev.snapshot_interval
-        self.hb = hb
-        need = C.c_longlong(0)
-        nat.check(ev.lib.ks_host_workspace_bytes(C.byref(self.plan), C.byref(hb), C.byref(need)))
-        self.workspace = torch.empty(int(need.value), dtype=torch.uint8, device=ev.device)
+        self.calls = []
+        for (m, a, b), plan in zip(t.parts, self.plans):
+            hb = nat.KsHostBatch()
+            hb.traces = self.h_traces
+            hb.n_traces = len(ev.traces)
+            hb.ep_policy = self.h_pol.data_ptr() + 4 * a
+            hb.ep_const = self.h_cof.data_ptr() + 4 * a
+            hb.consts = self.h_kf.data_ptr()
+            hb.n_consts = int(t.bound.consts.size)
+            hb.ep_trace = self.h_tr.data_ptr() + 4 * a
+            hb.nconst = self.h_nconst.data_ptr()
+            hb.results = self.h_res.data_ptr() + rec * a
+            hb.placements = None
+            hb.place_off = None
+            hb.placements_len = 0
+            for k in range(4):
+                hb.totals[k] = int(totals[k])
+            hb.max_events = 0
+            hb.snapshot_interval = ev.snapshot_interval
+            need = C.c_longlong(0)
+            nat.check(ev.lib.ks_host_workspace_bytes(C.byref(plan), C.byref(hb), C.byref(need)))
+            ws = torch.empty(int(need.value), dtype=torch.uint8, device=ev.device)
+            self.calls.append((m.program, plan, hb, ws))
+        self.hb = self.calls[0][2]
+        self.workspace = self.calls[0][3]
         self.h2d_bytes = 0
         self.d2h_bytes = 0
+        self._pool = None
+
+    def _one(self, call, cuda_stream):
+        prog, plan, hb, ws = call
+        up, down = C.c_longlong(0), C.c_longlong(0)
+        rc = self.ev.lib.ks_eval_batch_host(prog, C.byref(plan), C.byref(hb), C.c_void_p(ws.data_ptr()), ws.numel(),
+                                            C.c_void_p(cuda_stream), C.byref(up), C.byref(down))
+        return rc, (self.ev.lib.ks_last_error().decode(errors="replace") if rc else ""), up.value, down.value
 
     def run(self, stream=None) -> np.ndarray:
         """Host buffers in, host results out; returns the KsResult records (numpy structured array)."""
         torch = self.ev._torch
         st = stream or torch.cuda.current_stream(self.ev.device)
-        up, down = C.c_longlong(0), C.c_longlong(0)
-        nat.check(self.ev.lib.ks_eval_batch_host(self.prog, C.byref(self.plan), C.byref(self.hb),
-                                                 C.c_void_p(self.workspace.data_ptr()), self.workspace.numel(),
-                                                 C.c_void_p(st.cuda_stream), C.byref(up), C.byref(down)))
-        self.h2d_bytes, self.d2h_bytes = up.value, down.value
+        if len(self.calls) == 1:
+            outs = [self._one(self.calls[0], st.cuda_stream)]
+        else:
+            # each call copies, launches and waits for its own stream: run them from threads (ctypes releases the GIL)
+            import concurrent.futures as cf
+            if self._pool is None:
+                self._pool = cf.ThreadPoolExecutor(len(self.calls))
+            st.synchronize()
+            side = self.ev._side_streams(len(self.calls))
+            outs = list(self._pool.map(lambda cs: self._one(cs[0], cs[1].cuda_stream), zip(self.calls, side)))
+        for rc, msg, _u, _d in outs:
+            if rc:
+                raise nat.KsError(rc, msg)
+        self.h2d_bytes, self.d2h_bytes = sum(o[2] for o in outs), sum(o[3] for o in outs)
         res = np.frombuffer(self.h_res.numpy(), dtype=nat.RESULT_DTYPE)
         return res if self.order is None else res[self.inverse]
 

@@ -257,6 +257,23 @@ def _parse_expr(text: str) -> ast.expr:
     return ast.parse(text, mode="eval").body
 
 
+def _template_ending(fn: ast.FunctionDef) -> None:
+    """Every policy the reference's generator produces is the template filled in (safe_execution.py:171-224,283-317),
+    so it ends with `return max(1, int(score))`: a feasible node never scores 0.  Mutants of the hand-written baselines
+    that return a raw number get the same ending (without it a negative term makes feasible nodes score 0 and the pod
+    retries at every deletion: 2 M events instead of 20 k)."""
+    last = fn.body[-1] if fn.body else None
+    if not isinstance(last, ast.Return) or last.value is None:
+        return
+    v = last.value
+    if isinstance(v, ast.Call) and isinstance(v.func, ast.Name) and v.func.id == "max" and len(v.args) == 2 \
+            and isinstance(v.args[0], ast.Constant) and v.args[0].value == 1:
+        return
+    last.value = ast.Call(func=ast.Name(id="max", ctx=ast.Load()),
+                          args=[ast.Constant(value=1),
+                                ast.Call(func=ast.Name(id="int", ctx=ast.Load()), args=[v], keywords=[])], keywords=[])
+
+
 def mutate_source(src: str, rng: random.Random, n_mutations: int = 1) -> str:
     """`src` with n_mutations random edits applied (each one of the kinds listed in the module docstring).  The feasibility
     guards at the top of the function are left alone, so a mutant stays a policy that places pods."""
@@ -325,6 +342,7 @@ def mutate_source(src: str, rng: random.Random, n_mutations: int = 1) -> str:
             if cs:
                 n = rng.choice(cs)
                 n.ops[0] = {ast.Lt: ast.LtE, ast.LtE: ast.Lt, ast.Gt: ast.GtE, ast.GtE: ast.Gt}[type(n.ops[0])]()
+    _template_ending(fn)
     ast.fix_missing_locations(tree)
     return ast.unparse(tree) + "\n"
 

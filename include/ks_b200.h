@@ -87,6 +87,13 @@ int ks_set_cache_dir(const char* path);
  * Replaces: handing a scorer to KubernetesSimulator(..., scheduler=...) (simulator/main.py:29-41). */
 int ks_program_link(int n_policies, const long long* policies, long long* program);
 int ks_program_release(long long program);
+/* The two halves of ks_program_link for hosts that link in helper processes while the GPU process does other work (a
+ * fresh generation's structures are compiled AND linked by the compile workers, one module per worker): the first
+ * writes the linked, loadable image to a file and needs no GPU; the second loads an image.  `policies` must name the
+ * same structures in the same order on both sides (handles are per process).  Replaces the same step of the reference
+ * as ks_program_link (simulator/main.py:29-41). */
+int ks_program_link_image(int n_policies, const long long* policies, const char* path);
+int ks_program_load_image(const void* image, long long bytes, int n_policies, const long long* policies, long long* program);
 /* Link only (no device needed): proves every policy symbol resolves against the replay kernel. */
 int ks_program_link_check(int n_policies, const long long* policies, long long* linked_bytes);
 

@@ -154,6 +154,68 @@ def test_policy_major_table_and_two_ctas_per_sm(env):
         assert abs(dense["policy_score"][e] - ref.score) <= 1e-9 * max(abs(ref.score), 1e-300), e
 
 
+def test_batch_spread_over_several_modules_equals_one_module(env):
+    """A generation whose structures live in several linked modules (what the compile workers produce: one module per
+    worker) is replayed by one launch per module, in flight together; every result equals the single-module replay and
+    the oracle, through all three call forms."""
+    import numpy as np
+    from helpers import oracle_specs
+    from oracle import pysim
+    from funsearch_kubernetes_simulator_b200.variants import policy_population
+    cluster = env["ClusterSpec"].load("gpu16")
+    traces = [env["Trace"].load("default").head(900), env["Trace"].load("cpu200").head(700)]
+    pop = policy_population(40, seed=17)
+    ev = env["BatchEvaluator"](cluster, traces)
+    ev.module_structures = 5
+    compiled = ev.compile(pop, processes=0)
+    ep_pol = [p for p in range(40) for _ in range(2)]
+    ep_tr = [t for _ in range(40) for t in range(2)]
+    rb = ev.prepare_resident(compiled, ep_pol, ep_tr)
+    assert rb.n_modules >= 4 and len({p.teams_per_block for p in rb.plans}) == 1
+    rb.launch()
+    many = rb.results()
+    ev1 = env["BatchEvaluator"](cluster, traces)
+    rb1 = ev1.prepare_resident(ev1.compile(pop, processes=0), ep_pol, ep_tr)
+    assert rb1.n_modules == 1
+    rb1.launch()
+    one = rb1.results()
+    for f in many.dtype.names:
+        if f not in ("device_cycles", "reserved"):
+            assert np.array_equal(many[f], one[f]), f
+    assert np.array_equal(rb.scores_tensor().cpu().numpy(), one["policy_score"])
+    hb = ev.prepare_host_batch(compiled, ep_pol, ep_tr)
+    assert len(hb.calls) == rb.n_modules
+    host = hb.run()
+    for f in ("status", "events", "attempts", "placed", "policy_score"):
+        assert np.array_equal(host[f], one[f]), f
+    outs = ev.run_episodes(compiled, ep_pol, ep_tr, want_placements=True)
+    from helpers import outcome_digest
+    for e in (0, 7, 38, 79):
+        cs, ts = oracle_specs(cluster, traces[ep_tr[e]])
+        ref = pysim.run_episode(cs, ts, pysim.scorer_from_source(pop[ep_pol[e]]))
+        assert (outs[e].status, outs[e].events, outs[e].attempts, outs[e].placed) == (ref.status, ref.events, ref.attempts, ref.placed), e
+        if ref.status == 0:
+            assert outcome_digest(traces[ep_tr[e]], cluster, outs[e]) == pysim.placement_digest(ts, cs, ref), e
+        assert abs(outs[e].policy_score - ref.score) <= 1e-9 * max(abs(ref.score), 1e-300), e
+
+
+def test_generation_compiled_and_linked_by_the_worker_pool(env):
+    """A fresh generation through evaluate_population with the worker pool: translation, NVRTC and linking happen in the
+    workers (one module per worker), this process loads the modules; scores equal the in-process path's."""
+    from funsearch_kubernetes_simulator_b200.variants import policy_population
+    cluster = env["ClusterSpec"].load("gpu16")
+    tr = env["Trace"].load("default").head(600)
+    pop = policy_population(96, seed=23)
+    ev = env["BatchEvaluator"](cluster, [tr], processes=4)
+    got = ev.evaluate_population(pop)
+    st = ev.last_compile_stats
+    assert st["pool_workers"] == 4 and st["modules_loaded"] >= 2 and st["new_structures"] >= 48, st
+    ev1 = env["BatchEvaluator"](cluster, [tr], processes=0)
+    from funsearch_kubernetes_simulator_b200 import policy_compiler
+    want = ev1.evaluate_population(pop)
+    assert got == want and sum(1 for x in got if x > 0) > 60
+
+
 def test_host_buffer_entry_point_matches_resident_path(env):
     """ks_eval_batch_host (pinned host buffers) == ks_eval_batch (buffers resident in HBM)."""
     import numpy as np

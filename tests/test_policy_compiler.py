@@ -116,3 +116,32 @@ def test_variant_population_is_deterministic_and_translatable():
     a = policy_population(64, seed=3)
     assert a == policy_population(64, seed=3) and len(set(a)) == 64
     assert a != policy_population(64, seed=4)
+
+
+def test_compile_pool_translates_compiles_and_links_without_a_gpu(built_lib, tmp_path):
+    """The two phases a fresh generation goes through in the worker processes: sources -> (structure, float literals),
+    then new structures -> NVRTC programs -> one linked, loadable module image per worker.  No GPU is needed for any of it."""
+    from funsearch_kubernetes_simulator_b200 import compile_pool
+    from funsearch_kubernetes_simulator_b200.policy_compiler import compile_policy
+    from funsearch_kubernetes_simulator_b200.variants import policy_population
+    pop = policy_population(24, seed=9) + ["def priority_function(pod, node):\n    return {}\n"]
+    try:
+        compile_pool.start(2, 8)
+        info = compile_pool.wait_ready()
+        assert info["workers"] == 2
+        res, secs = compile_pool.run_jobs("translate", [pop[:12], pop[12:]])
+        assert all(r is not None for r in res) and len(secs) == 2
+        flat = res[0] + res[1]
+        assert flat[-1][0] == "error" and "Dict" in flat[-1][1]
+        for src, r in zip(pop[:-1], flat[:-1]):
+            cp = compile_policy(src)
+            assert (r[1], r[2], tuple(r[3])) == (cp.symbol, cp.flags, cp.consts) and r[0] == cp.cuda_source
+        structs = list({r[1]: (r[0], r[1], r[2]) for r in flat[:-1]}.values())
+        groups = [structs[i:i + 8] for i in range(0, len(structs), 8)]
+        img = str(tmp_path / "module.cubin")
+        out, _ = compile_pool.run_jobs("nvrtc_link", [(groups, img)])
+        assert out[0]["linked"] and all(x == 0 for st in out[0]["status"] for x in st)
+        import os
+        assert os.path.getsize(img) > 100000 and open(img, "rb").read(4) == b"\x7fELF"
+    finally:
+        compile_pool.shutdown()
