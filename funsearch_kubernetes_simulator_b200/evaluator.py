@@ -127,8 +127,7 @@ class BatchEvaluator:
     POOL_SOURCES = 48           # fresh sources from which translating in the pool pays off
     POOL_STRUCTURES = 24        # new structures from which NVRTC + link in the pool pays off
     MAX_MODULES = 64            # loaded modules kept (least recently used ones are released)
-    MAX_PARTS = 20              # modules one batch may be spread over before its structures are relinked into one
-    SINGLE_MODULE_WAVES = 8     # batches this many waves long are relinked into one module (one tail instead of many)
+    MAX_PARTS = 32              # modules one batch may be spread over; beyond, the smallest contributions are merged
 
     def __init__(self, cluster: ClusterSpec, traces: Sequence[Trace], device: int = 0,
                  snapshot_interval: float = 0.05, cache_dir: Optional[str] = None, processes: Optional[int] = None):
@@ -244,11 +243,21 @@ class BatchEvaluator:
             structs = list(new.values())
             groups = [structs[i:i + self.COMPILE_BATCH] for i in range(0, len(structs), self.COMPILE_BATCH)]
             if use_pool and len(structs) >= self.POOL_STRUCTURES and len(groups) > 1:
-                nw = max(1, compile_pool.n_workers())
-                if len(groups) < nw:   # fewer programs than workers: smaller programs, all workers busy
-                    g = max(4, -(-len(structs) // nw))
-                    groups = [structs[i:i + g] for i in range(0, len(structs), g)]
-                per_worker = [groups[i::nw] for i in range(nw) if groups[i::nw]]
+                # Deal the structures to the workers longest-first by source size (NVRTC time grows with it), then cut
+                # each worker's share into programs of at most COMPILE_BATCH: every worker ends at about the same time.
+                nw = max(1, min(compile_pool.n_workers(), -(-len(structs) // 4)))
+                shares: List[list] = [[] for _ in range(nw)]
+                load = [0] * nw
+                for st_ in sorted(structs, key=lambda x: -len(x[0])):
+                    k = load.index(min(load))
+                    shares[k].append(st_)
+                    load[k] += len(st_[0]) + 2000
+                per_worker = []
+                for sh in shares:
+                    n_prog = -(-len(sh) // self.COMPILE_BATCH)
+                    size = -(-len(sh) // n_prog)
+                    per_worker.append([sh[i:i + size] for i in range(0, len(sh), size)])
+                groups = [g for gs in per_worker for g in gs]
                 images = [os.path.join(compile_pool.cache_dir(), f"module_{os.getpid()}_{self._clock}_{k}.cubin")
                           for k in range(len(per_worker))]
                 self._clock += 1
@@ -348,10 +357,23 @@ class BatchEvaluator:
         cap = min(nat.KS_MAX_TABLE, self.module_structures or nat.KS_MAX_TABLE)
         for i in range(0, len(missing), cap):
             self._link_module(missing[i:i + cap])
-        used = {id(self._module_of[h]) for h in need}
-        if (len(used) > self.MAX_PARTS or (single_module and len(used) > 1)) and not self.module_structures:
+        used: dict = {}
+        for h in need:
+            used.setdefault(id(self._module_of[h]), []).append(h)
+        if single_module and len(used) > 1 and not self.module_structures:
             for i in range(0, len(need), nat.KS_MAX_TABLE):
                 self._link_module(need[i:i + nat.KS_MAX_TABLE])   # newest module wins in _module_of
+        elif len(used) > self.MAX_PARTS and not self.module_structures:
+            # Elites and re-tuned survivors of many earlier generations: each old module contributes a few structures.
+            # The smallest contributions are relinked into one module (cost ~ what is moved) until 3/4 of the limit.
+            moved, left = [], len(used)
+            for hs in sorted(used.values(), key=len):
+                if left + 1 <= self.MAX_PARTS * 3 // 4:
+                    break
+                moved.extend(hs)
+                left -= 1
+            for i in range(0, len(moved), nat.KS_MAX_TABLE):
+                self._link_module(moved[i:i + nat.KS_MAX_TABLE])
         mods: List[Module] = []
         index = {}
         self._clock += 1
@@ -583,8 +605,8 @@ class _Tables:
         if self.n_ep == 0 or ep_policy.min() < 0 or ep_policy.max() >= len(policies) or ep_trace.min() < 0 \
                 or ep_trace.max() >= len(ev.traces):
             raise ValueError("episode table is empty or refers to an unknown policy or trace")
-        if single_module is None:   # long batches: one module, one tail (the relink is small next to the run)
-            single_module = self.n_ep >= ev.SINGLE_MODULE_WAVES * 8 * ev.sm_count
+        if single_module is None:   # batches of several waves: one module, one tail, and the two-CTAs-per-SM kernel
+            single_module = self.n_ep >= 2 * 16 * ev.sm_count   # (the relink is small next to such a run)
         self.bound = bound = ev.bind(policies, pin=pin, single_module=single_module)
         part = bound.part[ep_policy]
         self.ep_slot = bound.slot[ep_policy]
