@@ -207,7 +207,7 @@ class BatchEvaluator:
         fresh = [s for s in dict.fromkeys(sources) if policy_compiler.cached(s) is None and s not in self._errors]
         stats["fresh_sources"] = len(fresh)
         if use_pool and len(fresh) >= self.POOL_SOURCES:
-            nw = compile_pool.n_workers()
+            nw = max(1, min(compile_pool.n_workers(), self.processes if processes is None else processes))
             per = -(-len(fresh) // nw)
             slices = [fresh[i:i + per] for i in range(0, len(fresh), per)]
             results, secs = compile_pool.run_jobs("translate", slices)
@@ -245,7 +245,8 @@ class BatchEvaluator:
             if use_pool and len(structs) >= self.POOL_STRUCTURES and len(groups) > 1:
                 # Deal the structures to the workers longest-first by source size (NVRTC time grows with it), then cut
                 # each worker's share into programs of at most COMPILE_BATCH: every worker ends at about the same time.
-                nw = max(1, min(compile_pool.n_workers(), -(-len(structs) // 4)))
+                nw = max(1, min(compile_pool.n_workers(), self.processes if processes is None else processes,
+                                -(-len(structs) // 4)))
                 shares: List[list] = [[] for _ in range(nw)]
                 load = [0] * nw
                 for st_ in sorted(structs, key=lambda x: -len(x[0])):
@@ -332,6 +333,7 @@ class BatchEvaluator:
                         if h in other.slot_of:
                             self._module_of[h] = other
                             break
+            self._torch.cuda.synchronize(self.device)   # no kernel of the module may still be running
             self.lib.ks_program_release(old.program)
         return m
 
@@ -353,10 +355,20 @@ class BatchEvaluator:
                 raise ValueError("policy was not compiled by BatchEvaluator.compile")
             handles.append(int(p.handle))
         need = sorted(set(handles))
-        missing = [h for h in need if h not in self._module_of]
         cap = min(nat.KS_MAX_TABLE, self.module_structures or nat.KS_MAX_TABLE)
-        for i in range(0, len(missing), cap):
-            self._link_module(missing[i:i + cap])
+        for _attempt in range(4):
+            # the modules this batch already lives in are the most recently used ones from here on: linking below may
+            # evict old modules, but not these
+            self._clock += 1
+            for h in need:
+                m = self._module_of.get(h)
+                if m is not None:
+                    m.last_use = self._clock
+            missing = [h for h in need if h not in self._module_of]
+            if not missing:
+                break
+            for i in range(0, len(missing), cap):
+                self._link_module(missing[i:i + cap])
         used: dict = {}
         for h in need:
             used.setdefault(id(self._module_of[h]), []).append(h)

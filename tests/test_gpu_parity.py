@@ -209,7 +209,7 @@ def test_generation_compiled_and_linked_by_the_worker_pool(env):
     ev = env["BatchEvaluator"](cluster, [tr], processes=4)
     got = ev.evaluate_population(pop)
     st = ev.last_compile_stats
-    assert st["pool_workers"] == 4 and st["modules_loaded"] >= 2 and st["new_structures"] >= 48, st
+    assert st["pool_workers"] >= 2 and 2 <= st["modules_loaded"] <= 4 and st["new_structures"] >= 48, st
     ev1 = env["BatchEvaluator"](cluster, [tr], processes=0)
     from funsearch_kubernetes_simulator_b200 import policy_compiler
     want = ev1.evaluate_population(pop)
