@@ -51,6 +51,7 @@
 #define KS_NC_CPU_TOTAL 0
 #define KS_NC_MEM_TOTAL 1
 #define KS_NC_NUM_GPUS 2
+#define KS_NC_TYPE 3             // index of the first node with an identical constant row ("node type"), set by ks_cluster_pack
 #define KS_NC_GPU_MILLI_TOTAL 4  // .. +7
 #define KS_NC_GPU_MEM_TOTAL 12   // .. +7   (GPU.memory_mib_total == memory_mib_left: never mutated)
 #define KS_NC_FIELDS 20
@@ -140,6 +141,7 @@ struct KsLaunch {
   int n_episodes;
   int n_nodes;
   int n_pad;
+  int class_slots;        // teams of warps: entries of the node-class table in shared memory (a power of two >= 2 * n_pad)
   int heap_smem_entries;  // reserved (0): the heap lives in the team's scratch, L1-resident
   int wait_smem_entries;  // reserved (0)
   int max_pods;           // largest n_pods over the traces of this batch (sizes the scratch regions)
