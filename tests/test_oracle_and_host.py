@@ -153,7 +153,11 @@ def test_cluster_pack(built_lib):
     assert rows[:16, 0].tolist() == c.cpu_total.tolist()
     assert rows[:16, 2].tolist() == c.num_gpus.tolist()
     assert rows[:16, 4:12].tolist() == c.gpu_milli_total.tolist() and rows[:16, 12:20].tolist() == c.gpu_mem_total.tolist()
-    assert not rows[16:].any() and not rows[:, 3].any()
+    assert not rows[16:].any()
+    # slot 3 = node type: the index of the first node with an identical constant row (10 x P100 nodes, 2 x V100M32 ...)
+    ty = rows[:16, 3].tolist()
+    assert all(ty[i] <= i and rows[ty[i]].tolist()[:3] + rows[ty[i]].tolist()[4:] == rows[i].tolist()[:3] + rows[i].tolist()[4:]
+               for i in range(16)) and len(set(ty)) == 5 and ty[0] == 0
     big = ClusterSpec.load("all1523").head(1024)
     assert big.n_pad == 1024 and big.packed()[1][2] == int(big.num_gpus.sum())
 

@@ -35,6 +35,16 @@ for W in widths:
     r = rb.results()
     cyc = r["device_cycles"].astype(float)
     ev_ = np.maximum(r["events"].astype(float), 1)
+    pa, pb = r["reserved"][:, 0].astype(float), r["reserved"][:, 1].astype(float)
+    if pa.sum() or pb.sum():
+        at = np.maximum(r["attempts"].astype(float), 1)
+        print(f"   phase clocks (KS_PHASE_CLOCKS={os.environ.get('KS_PHASE_CLOCKS')}): a/event {np.mean(pa / ev_):.0f}  b/event {np.mean(pb / ev_):.0f}  "
+              f"a/attempt {np.mean(pa / at):.0f}  b/attempt {np.mean(pb / at):.0f}  max_wait mean {r['max_waiting'].mean():.0f} "
+              f"frag events/ep {r['num_fragmentation_events'].mean():.0f}")
+    for i in np.argsort(-cyc)[:3]:
+        print(f"   slow ep {i}: {cyc[i] / 1e6:.0f} Mcyc events {r['events'][i]} attempts {r['attempts'][i]} frag {r['num_fragmentation_events'][i]} "
+              f"cyc/event {cyc[i] / ev_[i]:.0f} hoisted {compiled[i].flags} consts {len(compiled[i].consts)} src lines {pop[i].count(chr(10))}")
+    print(f"   all episodes: sum(cyc)/sum(events) = {cyc.sum() / ev_.sum():.0f}")
     print(f"W={W:2d} teams/blk {rb.plan.teams_per_block} blocks {rb.plan.blocks} smem/blk {rb.plan.smem_per_block}: {ms:9.1f} ms  "
           f"placements/s {r['placed'].sum() / ms * 1e3:.3e} | events/ep {ev_.mean():.0f} attempts/ep {r['attempts'].mean():.0f} "
           f"cyc/event mean {np.mean(cyc / ev_):.0f} slowest ep {cyc.max() / 1e6:.0f} Mcyc  status ok {int((r['status'] == 0).sum())}/64",
