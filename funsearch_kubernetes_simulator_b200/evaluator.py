@@ -128,6 +128,7 @@ class BatchEvaluator:
     POOL_STRUCTURES = 24        # new structures from which NVRTC + link in the pool pays off
     MAX_MODULES = 64            # loaded modules kept (least recently used ones are released)
     MAX_PARTS = 32              # modules one batch may be spread over; beyond, the smallest contributions are merged
+    CONSOLIDATE_PARTS = 6       # a batch spread over more modules than this is relinked into ONE module in the background
 
     def __init__(self, cluster: ClusterSpec, traces: Sequence[Trace], device: int = 0,
                  snapshot_interval: float = 0.05, cache_dir: Optional[str] = None, processes: Optional[int] = None):
@@ -161,6 +162,8 @@ class BatchEvaluator:
         self._module_of: dict = {}     # structure handle -> newest module holding it
         self._pinned: set = set()
         self._clock = 0
+        self._bg_thread = None         # background relink of the last generation's structures into one module
+        self._bg_done: list = []       # finished relinks: (handles in table order, program), adopted by the next bind()
         self._streams: list = []
         self._errors: dict = {}
         self.last_plan = None
@@ -337,6 +340,39 @@ class BatchEvaluator:
             self.lib.ks_program_release(old.program)
         return m
 
+    def _adopt_consolidated(self) -> None:
+        """Modules linked in the background become the home of their structures (the small per-worker modules they
+        replace age out of the cache)."""
+        while self._bg_done:
+            order, prog = self._bg_done.pop()
+            self._add_module(Module(prog, {h: i for i, h in enumerate(order)}))
+
+    def _consolidate_async(self, handles: Sequence[int]) -> None:
+        """Relink `handles` into one module on a helper thread (nvJitLink and the module load release the GIL).  The
+        compile workers hand a fresh generation over as one module per worker, which is what makes the first
+        evaluation fast; between generations -- while the caller's LLM writes the next one -- the generation is merged,
+        so that a later batch finds last generation's survivors in one module, not in sixteen."""
+        import threading
+        if self._bg_thread is not None and self._bg_thread.is_alive():
+            return
+        order = sorted(set(handles))
+        if len(order) > nat.KS_MAX_TABLE or len(order) < 2:
+            return
+
+        def work():
+            arr = (C.c_longlong * len(order))(*order)
+            out = C.c_longlong(-1)
+            if self.lib.ks_program_link(len(order), arr, C.byref(out)) == 0:
+                self._bg_done.append((order, out.value))
+        self._bg_thread = threading.Thread(target=work, daemon=True)
+        self._bg_thread.start()
+
+    def wait_background(self) -> None:
+        """Block until a background relink (if any) has finished and adopt its module."""
+        if self._bg_thread is not None:
+            self._bg_thread.join()
+        self._adopt_consolidated()
+
     def _link_module(self, handles: Sequence[int]) -> Module:
         order = sorted(set(handles))
         arr = (C.c_longlong * len(order))(*order)
@@ -355,6 +391,7 @@ class BatchEvaluator:
                 raise ValueError("policy was not compiled by BatchEvaluator.compile")
             handles.append(int(p.handle))
         need = sorted(set(handles))
+        self._adopt_consolidated()
         cap = min(nat.KS_MAX_TABLE, self.module_structures or nat.KS_MAX_TABLE)
         for _attempt in range(4):
             # the modules this batch already lives in are the most recently used ones from here on: linking below may
@@ -401,6 +438,8 @@ class BatchEvaluator:
                     self._pinned.add(m.program)
             part[k] = index[id(m)]
             slot[k] = m.slot_of[h]
+        if len(mods) > self.CONSOLIDATE_PARTS and not self.module_structures:
+            self._consolidate_async(need)
         lens = np.array([len(p.consts) for p in policies], dtype=np.int64)
         off = np.concatenate([[0], np.cumsum(lens)[:-1]]) if len(policies) else np.zeros(0, np.int64)
         if lens.sum() >= 2 ** 31:

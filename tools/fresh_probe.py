@@ -35,4 +35,6 @@ for k in range(gens):
         print(ok[worst].source)
     t0 = time.perf_counter()
     ev.evaluate_population(pop)
-    print(f"   evaluate_population again (everything cached): {time.perf_counter() - t0:.3f} s")
+    print(f"   evaluate_population again (everything cached): {time.perf_counter() - t0:.3f} s, modules loaded {len(ev._modules)}")
+    if len(sys.argv) > 2:
+        time.sleep(float(sys.argv[2]))   # the caller's think time between generations (the background relink uses it)
