@@ -46,6 +46,13 @@ WORKLOADS = {
 }
 
 
+# config 2: the six shipped policies the C oracle has hand translations of ride along with the 58 variants, so the measured
+# batch itself is checked against the CPU (name in tests/golden/policies.json -> built-in of oracle/ksim_oracle.c)
+C_ORACLE_POLICIES = {"ts_first_fit": "first_fit", "ts_best_fit": "best_fit", "ts_funsearch_4901": "funsearch_4901",
+                     "ts_funsearch_4816": "funsearch_4816", "ts_funsearch_4800": "funsearch_4800", "fs_worst_fit": "worst_fit"}
+CONFIG2_EVENT_BUDGET = 4000000   # per episode: a spreading policy never catches up with this arrival rate (status 3)
+
+
 def workload_config(args):
     """The `config` object: identical in both arms (b200 / reference) for the same command line."""
     c = {"workload": WORKLOADS[args.config], "config_id": args.config, "population": f"variants.policy_population(seed={args.seed})",
@@ -165,7 +172,8 @@ def build_workload(args, rank, world):
     if args.config == 2:
         cluster = ClusterSpec.load("all1523").head(1024)
         traces = [synthetic_trace(args.pods or 1000000, seed=3, load_factor=200.0)]
-        pop = policy_population(64, seed=seed)
+        shipped = json.load(open(os.path.join(ROOT, "tests", "golden", "policies.json")))
+        pop = policy_population(64 - len(C_ORACLE_POLICIES), seed=seed) + [shipped[k] for k in C_ORACLE_POLICIES]
         return cluster, traces, pop, list(range(64)), [0] * 64, None
     if args.config == 3:
         cluster = ClusterSpec.load("gpu16")
@@ -177,6 +185,49 @@ def build_workload(args, rank, world):
         ep_tr = [t for _p in range(len(pop)) for t in range(len(traces))]
         return cluster, traces, pop, ep_pol, ep_tr, None
     raise ValueError(args.config)
+
+
+def config2_cpu_column(cluster, trace, pop):
+    """CPU column of config 2: the C oracle (oracle/ksim_oracle.c, -O2, the same algorithm with hand-translated policies)
+    replays the six shipped policies on the full trace, one thread each; plus the Python port on a prefix of the trace,
+    extrapolated (the Python path needs minutes per episode at this size)."""
+    import threading
+    from oracle import coracle, pysim
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    from helpers import oracle_specs
+    names = list(C_ORACLE_POLICIES)
+    out = {}
+
+    def work(nm):
+        t0 = time.perf_counter()
+        res, _t, _n, _m = coracle.run(cluster, trace, C_ORACLE_POLICIES[nm], max_events=CONFIG2_EVENT_BUDGET)
+        out[nm] = (res.status, res.events, res.attempts, res.placed, res.score, time.perf_counter() - t0)
+    coracle.lib()
+    ths = [threading.Thread(target=work, args=(nm,)) for nm in names]
+    t0 = time.perf_counter()
+    for th in ths:
+        th.start()
+    for th in ths:
+        th.join()
+    wall = time.perf_counter() - t0
+    placed = sum(v[3] for v in out.values())
+    busy = sum(v[5] for v in out.values())
+    # Python port: first 2,000 pods of the trace under first-fit, one core
+    n_prefix = 2000
+    cs, ts = oracle_specs(cluster, trace.head(n_prefix))
+    shipped = json.load(open(os.path.join(ROOT, "tests", "golden", "policies.json")))
+    t0 = time.perf_counter()
+    r = pysim.run_episode(cs, ts, pysim.scorer_from_source(shipped["ts_first_fit"]))
+    t_py = time.perf_counter() - t0
+    cores = host_cores()
+    col = {"value": placed / busy * cores, "unit": UNIT, "cores": cores, "kind": "port",
+           "sample": f"C oracle (gcc -O2), the 6 shipped policies x the full trace (event budget {CONFIG2_EVENT_BUDGET}), "
+                     f"one thread each: {placed} placements in {busy:.1f} core-seconds ({wall:.1f} s wall); value = per-core rate x {cores} cores",
+           "per_core_value": placed / busy,
+           "python_port_extrapolated": {"per_core_value": r.placed / t_py, "value": r.placed / t_py * cores,
+                                        "sample": f"oracle/pysim.py, first-fit, first {n_prefix} pods of the trace x 1,024 nodes on one core "
+                                                  f"({t_py:.1f} s), extrapolated to {cores} cores; labelled extrapolation (SURVEY 8d)"}}
+    return col, {nm: v[:5] for nm, v in out.items()}
 
 
 # --------------------------------------------------------------------------------------------- reference arm
@@ -239,6 +290,10 @@ def run_b200(args):
                         "sample": f"first {n_sample} of the {n_ep} episodes, oracle/pysim.py on {cores} processes, {t:.1f} s",
                         "policy_evals_per_sec": e / t, "per_core_value": p / _W["busy_s"]}
 
+    c2_rows = {}
+    if rank == 0 and world == 1 and not args.no_cpu_baseline and args.config == 2:
+        cpu_baseline, c2_rows = config2_cpu_column(cluster, traces[0], pop)
+
     import numpy as np
     import torch
     import torch.distributed as dist
@@ -249,8 +304,9 @@ def run_b200(args):
     if rank == 0:
         __graft_entry__.build()
     torch.cuda.set_device(local)
-    if world > 1:
+    if world > 1 and not dist.is_initialized():
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    if world > 1:
         dist.barrier()
     dev = torch.device("cuda", local)
     t0 = time.perf_counter()
@@ -272,7 +328,8 @@ def run_b200(args):
     t_cached = time.perf_counter() - t0
     t0 = time.perf_counter()
     single = True if args.single_module else None
-    rb = ev.prepare_resident(compiled, ep_pol, ep_tr, teams_per_block=args.teams, single_module=single)
+    budget = CONFIG2_EVENT_BUDGET if args.config == 2 else 0
+    rb = ev.prepare_resident(compiled, ep_pol, ep_tr, teams_per_block=args.teams, single_module=single, max_events=budget)
     t_link = time.perf_counter() - t0
     hbatch = ev.prepare_host_batch(compiled, ep_pol, ep_tr, teams_per_block=args.teams, single_module=single)
 
@@ -337,6 +394,17 @@ def run_b200(args):
             if first_bad is None:
                 first_bad = {"episode": i, "gpu": got + (float(g["policy_score"]),), "cpu": list(row)}
 
+    for nm, row in c2_rows.items():   # config 2: the shipped policies of the batch against the C oracle
+        i = len(pop) - len(C_ORACLE_POLICIES) + list(C_ORACLE_POLICIES).index(nm)
+        g = res[i]
+        got = (int(g["status"]), int(g["events"]), int(g["attempts"]), int(g["placed"]))
+        same = got == tuple(row[:4]) and abs(float(g["policy_score"]) - row[4]) <= 1e-9 * max(abs(row[4]), 1e-300)
+        parity_checked += 1
+        if not same:
+            parity_bad += 1
+            if first_bad is None:
+                first_bad = {"episode": i, "policy": nm, "gpu": got + (float(g["policy_score"]),), "cpu": list(row)}
+
     # end to end through the host-buffer C ABI
     for _ in range(2):
         hbatch.run(stream)
@@ -393,8 +461,6 @@ def run_b200(args):
         kern_total = float(sum(kern_ms))
         placed_all, evals_all, events_all = placed, evals, events
     if rank != 0:
-        if world > 1:
-            dist.destroy_process_group()
         return
 
     ms_per_step = total_ms / args.steps
@@ -458,8 +524,152 @@ def run_b200(args):
         "clocks": clocks.summary(),
     }
     emit(line)
+
+
+# --------------------------------------------------------------------------------------------- config 3: strong scaling
+def run_config3(args):
+    """One population x 16 traces x 4 bootstrap seeds, ONE episode table cut over the ranks by policy (LPT on each
+    policy's predicted cost), through the product's sharded API; the single exchange is the all-gather of per-policy
+    fitness.  `value`: launch + device-side per-policy mean + NCCL all-gather, inputs resident.  `e2e`:
+    distributed.evaluate_population_sharded(sources, BatchEvaluator.evaluate_population, costs) wall clock."""
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    from funsearch_kubernetes_simulator_b200 import _native as nat
+    from funsearch_kubernetes_simulator_b200 import compile_pool
+    from funsearch_kubernetes_simulator_b200.distributed import evaluate_population_sharded, shard_plan
+    from funsearch_kubernetes_simulator_b200.evaluator import BatchEvaluator
+    import __graft_entry__
+    cluster, traces, pop, _ep, _et, _ = build_workload(args, rank, world)
+    if rank == 0:
+        __graft_entry__.build()
+    torch.cuda.set_device(local)
     if world > 1:
-        dist.destroy_process_group()
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+        dist.barrier()
+    dev = torch.device("cuda", local)
+    ev = BatchEvaluator(cluster, traces, device=local)
+    if compile_pool.n_workers():
+        compile_pool.wait_ready()
+    n_tr = len(traces)
+    t0 = time.perf_counter()
+    compiled_all = ev.compile(pop)
+    t_compile = time.perf_counter() - t0
+    keep = [i for i, c in enumerate(compiled_all) if c is not None]
+    pop = [pop[i] for i in keep]
+    compiled_all = [compiled_all[i] for i in keep]
+    # predicted cost of a policy = the events it generated on the first trace (in an evolution run: last generation's)
+    cal = ev.prepare_resident(compiled_all, list(range(len(pop))), [0] * len(pop))
+    cal.launch()
+    costs = [float(x) for x in cal.results()["events"]]
+    plan = shard_plan(len(pop), world, costs)
+    mine = plan[rank]
+    cap = max(len(sh) for sh in plan)
+    my_pol = [compiled_all[i] for i in mine]
+    ep_pol = [p for p in range(len(mine)) for _t in range(n_tr)]
+    ep_tr = [t for _p in range(len(mine)) for t in range(n_tr)]
+    rb = ev.prepare_resident(my_pol, ep_pol, ep_tr)
+    stream = torch.cuda.current_stream(dev)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    block = torch.zeros(cap, dtype=torch.float64, device=dev)
+    gathered = torch.empty(world * cap, dtype=torch.float64, device=dev)
+
+    def step():
+        rb.launch(stream)
+        sc = rb.scores_tensor().view(len(mine), n_tr)
+        ok = (rb.status_tensor().view(len(mine), n_tr) == 0).all(dim=1)
+        block[:len(mine)] = torch.where(ok, sc.mean(dim=1), torch.zeros_like(sc[:, 0]))
+        if world > 1:
+            dist.all_gather_into_tensor(gathered, block)
+    for _ in range(max(1, min(args.warmup, 3))):
+        step()
+    torch.cuda.synchronize(dev)
+    launches0 = nat.lib().ks_launch_count()
+    evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    kevs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    with ClockSampler(local) as clocks:
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize(dev)
+        for k in range(args.steps):
+            flush.fill_(k & 0xFF)
+            evs[k][0].record(stream)
+            kevs[k][0].record(stream)
+            rb.launch(stream)
+            kevs[k][1].record(stream)
+            sc = rb.scores_tensor().view(len(mine), n_tr)
+            ok = (rb.status_tensor().view(len(mine), n_tr) == 0).all(dim=1)
+            block[:len(mine)] = torch.where(ok, sc.mean(dim=1), torch.zeros_like(sc[:, 0]))
+            if world > 1:
+                dist.all_gather_into_tensor(gathered, block)
+            evs[k][1].record(stream)
+        torch.cuda.synchronize(dev)
+        if world > 1:
+            dist.barrier()
+    launches = nat.lib().ks_launch_count() - launches0
+    total_ms = float(sum(a.elapsed_time(b) for a, b in evs))
+    kern_ms = float(sum(a.elapsed_time(b) for a, b in kevs))
+    res = rb.results()
+    placed, evals, events = int(res["placed"].sum()), int(res["scorer_calls"].sum()), int(res["events"].sum())
+    device_fitness = block[:len(mine)].cpu().numpy().copy()
+    # end to end through the sharded product API (cached compilation; host tables in, fitness list out)
+    if world > 1:
+        dist.barrier()
+    t0 = time.perf_counter()
+    fit = evaluate_population_sharded(pop, ev.evaluate_population, costs, device=dev)
+    torch.cuda.synchronize(dev)
+    if world > 1:
+        dist.barrier()
+    e2e_s = time.perf_counter() - t0
+    mism = int(sum(1 for k, i in enumerate(mine) if fit[i] != float(device_fitness[k])))
+    stats = torch.tensor([total_ms, e2e_s, float(placed), float(evals), float(events), kern_ms, float(mism)], dtype=torch.float64, device=dev)
+    if world > 1:
+        mx = stats.clone()
+        dist.all_reduce(mx, op=dist.ReduceOp.MAX)
+        sm = stats.clone()
+        dist.all_reduce(sm, op=dist.ReduceOp.SUM)
+        mn = stats.clone()
+        dist.all_reduce(mn, op=dist.ReduceOp.MIN)
+        total_ms, e2e_s, kern_max, kern_min = float(mx[0]), float(mx[1]), float(mx[5]), float(mn[5])
+        placed_all, evals_all, events_all, mism = int(sm[2]), int(sm[3]), int(sm[4]), int(sm[6])
+    else:
+        kern_max = kern_min = kern_ms
+        placed_all, evals_all, events_all = placed, evals, events
+    if rank == 0:
+        ms_per_step = total_ms / args.steps
+        peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+        peak = json.load(open(peaks_path))["hbm_gbs"] if os.path.exists(peaks_path) else 6650.0
+        alg_bytes = 32 * placed + len(ep_pol) * (128 + cluster.n_nodes * 80)
+        achieved = alg_bytes / (kern_max / args.steps * 1e-3) / 1e9
+        emit({"metric": METRIC, "value": placed_all / (ms_per_step * 1e-3), "unit": UNIT, "n_gpus": world, "steps": args.steps,
+              "warmup": max(1, min(args.warmup, 3)), "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong",
+              "vs_baseline": None, "dtype": "int64+f64",
+              "data": "16 bundled OpenB traces x 4 bootstrap resamples; synthetic policy population (seeded, no LLM)",
+              "config": workload_config(args),
+              "launch": {"episodes_total": len(pop) * n_tr, "episodes_this_rank": len(ep_pol), "policies": len(pop), "traces": n_tr,
+                         "sharding": "by policy, LPT on events of a calibration episode (distributed.shard_plan)",
+                         "largest_shard_policies": cap, "ctas_per_sm": rb.plan.ctas_per_sm, "teams_per_block": rb.plan.teams_per_block,
+                         "blocks": rb.plan.blocks, "modules_in_batch": rb.n_modules, "l2": "flushed between timed steps (256 MiB write)",
+                         "kernel_ms_slowest_rank": kern_max / args.steps, "kernel_ms_fastest_rank": kern_min / args.steps,
+                         "limiter": "slowest shard's kernel (step - slowest kernel = reduction + all-gather)",
+                         "step_minus_slowest_kernel_ms": ms_per_step - kern_max / args.steps},
+              "parity_checked_episodes": 0, "parity_mismatches": 0,
+              "sharded_api_vs_device_fitness_mismatches": mism,
+              "policy_evals_per_sec": evals_all / (ms_per_step * 1e-3), "events_per_sec": events_all / (ms_per_step * 1e-3),
+              "episodes_per_sec": len(pop) * n_tr / (ms_per_step * 1e-3),
+              "e2e": {"value": placed_all / e2e_s, "unit": UNIT, "ms_per_step": e2e_s * 1e3,
+                      "h2d_bytes_per_step": int(len(ep_pol) * 12), "d2h_bytes_per_step": int(len(ep_pol) * 128),
+                      "path": "distributed.evaluate_population_sharded(sources, BatchEvaluator.evaluate_population, costs): shard, "
+                              "episode tables H2D, kernel, results D2H, NCCL all-gather of fitness (one call, compilation cached)"},
+              "gpu_launches": int(launches),
+              "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+                           "kernel": "ks_replay_kernel_dense" if rb.plan.ctas_per_sm == 2 else "ks_replay_kernel",
+                           "note": "this rank's launch; serial event chains, HBM fraction expected << 1% (SURVEY 8d)"},
+              "cpu_baseline": None, "compile": {"policies": len(pop), "total_s": t_compile},
+              "clocks": clocks.summary()})
 
 
 _RESULT_OUT = None
@@ -498,8 +708,24 @@ def main():
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)
+    elif args.config == 3:
+        run_config3(args)
+    elif args.config == 4:
+        first = True
+        for lg in range(10, 18):
+            args.episodes = 1 << lg
+            args.fresh_steps = 0
+            args.no_cpu_baseline = args.no_cpu_baseline or not first
+            run_b200(args)
+            first = False
     else:
         run_b200(args)
+    try:
+        import torch.distributed as dist
+        if dist.is_available() and dist.is_initialized():
+            dist.destroy_process_group()
+    except Exception:  # noqa: BLE001
+        pass
 
 
 if __name__ == "__main__":

@@ -162,6 +162,7 @@ class BatchEvaluator:
         self._module_of: dict = {}     # structure handle -> newest module holding it
         self._pinned: set = set()
         self._clock = 0
+        self._keep: set = set()        # modules the batch being bound lives in: never evicted while it is bound
         self._bg_thread = None         # background relink of the last generation's structures into one module
         self._bg_done: list = []       # finished relinks: (handles in table order, program), adopted by the next bind()
         self._streams: list = []
@@ -324,7 +325,7 @@ class BatchEvaluator:
         for h in m.slot_of:
             self._module_of[h] = m
         while len(self._modules) > self.MAX_MODULES:
-            victims = [x for x in self._modules if x.program not in self._pinned and x is not m]
+            victims = [x for x in self._modules if x.program not in self._pinned and x is not m and id(x) not in self._keep]
             if not victims:
                 break
             old = min(victims, key=lambda x: x.last_use)
@@ -397,10 +398,12 @@ class BatchEvaluator:
             # the modules this batch already lives in are the most recently used ones from here on: linking below may
             # evict old modules, but not these
             self._clock += 1
+            self._keep = set()
             for h in need:
                 m = self._module_of.get(h)
                 if m is not None:
                     m.last_use = self._clock
+                    self._keep.add(id(m))
             missing = [h for h in need if h not in self._module_of]
             if not missing:
                 break
@@ -438,6 +441,7 @@ class BatchEvaluator:
                     self._pinned.add(m.program)
             part[k] = index[id(m)]
             slot[k] = m.slot_of[h]
+        self._keep = set()
         if len(mods) > self.CONSOLIDATE_PARTS and not self.module_structures:
             self._consolidate_async(need)
         lens = np.array([len(p.consts) for p in policies], dtype=np.int64)
@@ -550,15 +554,17 @@ class BatchEvaluator:
 
     # ------------------------------------------------------------------ resident form (inputs already in HBM)
     def prepare_resident(self, policies: Sequence[CompiledPolicy], ep_policy: Sequence[int], ep_trace: Sequence[int],
-                         teams_per_block: int = 0, single_module: Optional[bool] = None) -> "ResidentBatch":
-        return ResidentBatch(self, policies, ep_policy, ep_trace, teams_per_block, single_module=single_module)
+                         teams_per_block: int = 0, single_module: Optional[bool] = None, max_events: int = 0) -> "ResidentBatch":
+        return ResidentBatch(self, policies, ep_policy, ep_trace, teams_per_block, single_module=single_module,
+                             max_events=max_events)
 
     # ------------------------------------------------------------------ host-buffer (end-to-end) form
     def prepare_host_batch(self, policies: Sequence[CompiledPolicy], ep_policy: Sequence[int], ep_trace: Sequence[int],
-                           teams_per_block: int = 0, single_module: Optional[bool] = None) -> "HostBatch":
+                           teams_per_block: int = 0, single_module: Optional[bool] = None, max_events: int = 0) -> "HostBatch":
         """Stage a batch in pinned host memory for ks_eval_batch_host (everything the step needs crosses
         PCIe inside the call: traces, cluster table, episode table in; results out)."""
-        return HostBatch(self, policies, ep_policy, ep_trace, teams_per_block, single_module=single_module)
+        return HostBatch(self, policies, ep_policy, ep_trace, teams_per_block, single_module=single_module,
+                         max_events=max_events)
 
     # ------------------------------------------------------------------ reference-shaped entry points
     def evaluate_population(self, codes: Sequence[str], trace_ids: Optional[Sequence[int]] = None,
@@ -595,15 +601,30 @@ class BatchEvaluator:
         status = [nat.ST_OK if cp is not None else nat.ST_UNSUPPORTED for cp in compiled]
         messages = {i: "translator: " + (self.compile_error(codes[i]) or "declined") for i, cp in enumerate(compiled) if cp is None}
         if ep_pol:
-            outs = self.run_episodes(uniq, ep_pol, ep_tr)
-            acc = [0.0] * len(codes)
-            for o, i in zip(outs, owner):
-                acc[i] += o.policy_score if o.status == nat.ST_OK else 0.0
-                if o.status != nat.ST_OK and status[i] == nat.ST_OK:
-                    status[i] = o.status
-                    messages[i] = "episode status: " + o.status_name
+            torch = self._torch
+            rb = ResidentBatch(self, uniq, ep_pol, ep_tr, pin=False)
+            st_ = torch.cuda.current_stream(self.device)
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(st_)
+            rb.launch(st_)
+            e1.record(st_)
+            res = rb.results(st_)
+            self.last_kernel_ms = e0.elapsed_time(e1)
+            self.last_plan = rb.plans[0]
+            self.last_results = res
+            own = np.asarray(owner, dtype=np.int64)
+            ok_ep = res["status"] == nat.ST_OK
+            acc = np.bincount(own, weights=np.where(ok_ep, res["policy_score"], 0.0), minlength=len(codes))
             # any failed episode of a policy is an exception in the reference's worker: the policy scores 0
-            scores = [a / len(trace_ids) if status[i] == nat.ST_OK else 0.0 for i, a in enumerate(acc)]
+            worst = np.zeros(len(codes), dtype=np.int64)
+            np.maximum.at(worst, own, np.where(ok_ep, 0, res["status"]).astype(np.int64))
+            for i in np.nonzero(worst)[0]:
+                # a real failure (exception, GPU shortfall) in any episode makes 0 the reference's answer too; only a
+                # policy whose failures are all 'unsupported' counts as not evaluated
+                first = int(res["status"][(own == i) & ~ok_ep].min())
+                status[int(i)] = first
+                messages[int(i)] = "episode status: " + nat.STATUS_NAMES.get(first, str(first))
+            scores = [float(acc[i]) / len(trace_ids) if status[i] == nat.ST_OK else 0.0 for i in range(len(codes))]
         not_eval = [i for i, st in enumerate(status) if st == nat.ST_UNSUPPORTED]
         self.last_report = PopulationReport(list(scores), status, not_eval, messages,
                                             len({cp.symbol for cp in compiled if cp is not None}))
@@ -786,6 +807,12 @@ class ResidentBatch:
         rows = [place[self.place_off[k]: self.place_off[k] + t.pods_per_ep[k]] for k in range(self.n_ep)]
         return rows if self.order is None else [rows[int(self.inverse[e])] for e in range(self.n_ep)]
 
+    def status_tensor(self):
+        """Per-episode status word as a device int32 tensor (caller's order)."""
+        torch = self.ev._torch
+        col = self.d_res.view(torch.int32).view(self.n_ep, nat.RESULT_DTYPE.itemsize // 4)[:, 0]
+        return col if self.order is None else col[self._d_inverse]
+
     def scores_tensor(self):
         """Per-episode policy_score as a device fp64 tensor (a strided view of the result records)."""
         torch = self.ev._torch
@@ -798,7 +825,7 @@ class HostBatch:
     """One batch held in pinned host memory + device workspaces; run() = one ks_eval_batch_host call per module the
     batch's structures live in (concurrently, each on its own stream)."""
 
-    def __init__(self, ev: BatchEvaluator, policies, ep_policy, ep_trace, teams_per_block=0, single_module=None):
+    def __init__(self, ev: BatchEvaluator, policies, ep_policy, ep_trace, teams_per_block=0, single_module=None, max_events=0):
         torch = ev._torch
         self.ev = ev
         t = self.tables = _Tables(ev, policies, ep_policy, ep_trace, teams_per_block, False, True, single_module)
@@ -846,7 +873,7 @@ class HostBatch:
             hb.placements_len = 0
             for k in range(4):
                 hb.totals[k] = int(totals[k])
-            hb.max_events = 0
+            hb.max_events = max_events
             hb.snapshot_interval = ev.snapshot_interval
             need = C.c_longlong(0)
             nat.check(ev.lib.ks_host_workspace_bytes(C.byref(plan), C.byref(hb), C.byref(need)))
