@@ -126,7 +126,7 @@ class BatchEvaluator:
     COMPILE_BATCH = 16          # structures per NVRTC program (ks_set_compile_batch)
     POOL_SOURCES = 48           # fresh sources from which translating in the pool pays off
     POOL_STRUCTURES = 24        # new structures from which NVRTC + link in the pool pays off
-    MAX_MODULES = 64            # loaded modules kept (least recently used ones are released)
+    MAX_MODULES = 128           # loaded modules kept (least recently used ones are released)
     MAX_PARTS = 32              # modules one batch may be spread over; beyond, the smallest contributions are merged
     CONSOLIDATE_PARTS = 6       # a batch spread over more modules than this is relinked into ONE module in the background
 
@@ -258,7 +258,11 @@ class BatchEvaluator:
                     shares[k].append(st_)
                     load[k] += len(st_[0]) + 2000
                 per_worker = []
-                for sh in shares:
+                for k, sh in enumerate(shares):
+                    # big and small structures alternate inside a module: table neighbours share an SM, and eight
+                    # 6 KB policies side by side thrash its instruction cache (measured: slowest episode +30 %)
+                    sh = [sh[(i // 2) if i % 2 == 0 else len(sh) - 1 - i // 2] for i in range(len(sh))]
+                    shares[k] = sh
                     n_prog = -(-len(sh) // self.COMPILE_BATCH)
                     size = -(-len(sh) // n_prog)
                     per_worker.append([sh[i:i + size] for i in range(0, len(sh), size)])
@@ -347,6 +351,12 @@ class BatchEvaluator:
         while self._bg_done:
             order, prog = self._bg_done.pop()
             self._add_module(Module(prog, {h: i for i, h in enumerate(order)}))
+            # modules all of whose structures now live elsewhere will never be bound again: release them
+            for old in [m for m in self._modules if m.program not in self._pinned and id(m) not in self._keep
+                        and all(self._module_of.get(h) is not m for h in m.slot_of)]:
+                self._modules.remove(old)
+                self._torch.cuda.synchronize(self.device)
+                self.lib.ks_program_release(old.program)
 
     def _consolidate_async(self, handles: Sequence[int]) -> None:
         """Relink `handles` into one module on a helper thread (nvJitLink and the module load release the GIL).  The
@@ -367,6 +377,12 @@ class BatchEvaluator:
                 self._bg_done.append((order, out.value))
         self._bg_thread = threading.Thread(target=work, daemon=True)
         self._bg_thread.start()
+        if not getattr(self, "_atexit", False):   # the helper thread must not be inside the linker when the process exits
+            import atexit
+            import weakref
+            ref = weakref.ref(self)
+            atexit.register(lambda: ref() is not None and ref()._bg_thread is not None and ref()._bg_thread.join())
+            self._atexit = True
 
     def wait_background(self) -> None:
         """Block until a background relink (if any) has finished and adopt its module."""
@@ -697,20 +713,39 @@ class _Tables:
         # one part per module: [start, end) of the sorted table
         cuts = [0] + [int(i) for i in np.nonzero(np.diff(part))[0] + 1] + [self.n_ep]
         self.parts = [(bound.modules[int(part[a])], a, b) for a, b in zip(cuts[:-1], cuts[1:])]
-        # geometry: the same number of episodes per CTA in every part, chosen so that all CTAs are resident together
+        # Geometry.  One module: ks_plan's own choice.  Several modules: the SMs are dealt to the parts in proportion to
+        # their episodes (at least one CTA each), with as many teams per CTA as a single launch of the whole table would
+        # use, so that all CTAs are resident together and every SM carries about the same number of episodes.  (A plan
+        # may carry any block count: the kernel cuts the part's table into one balanced range per CTA.)
         n_parts = len(self.parts)
-        dense_ok = n_parts == 1
-        tpb = teams_per_block
-        if n_parts > 1 and tpb == 0:
-            w = ev.warps_per_team or ev.plan(1, False, 1).warps_per_team
-            lim = max(1, (16 if w > 8 else 8) // max(1, w))
-            tpb = max(1, min(lim, -(-self.n_ep // ev.sm_count)))
-            while tpb < lim and sum(-(-(b - a) // tpb) for _m, a, b in self.parts) > ev.sm_count:
-                tpb += 1
         self.plans = []
-        for _m, a, b in self.parts:
-            self.plans.append(ev.plan(b - a, want_placements, int(self.pods_per_ep[a:b].max()), tpb,
-                                      episodes_per_policy=self.n_ep / self.n_structures, allow_dense=dense_ok))
+        if n_parts == 1:
+            self.plans.append(ev.plan(self.n_ep, want_placements, int(self.pods_per_ep.max()), teams_per_block,
+                                      episodes_per_policy=self.n_ep / self.n_structures))
+            return
+        whole = ev.plan(self.n_ep, False, 1, teams_per_block, allow_dense=False)
+        tpb = whole.teams_per_block
+        sizes = [b - a for _m, a, b in self.parts]
+        sms = ev.sm_count
+        if -(-self.n_ep // tpb) <= sms:      # everything fits in one wave: spread it over all SMs
+            blocks = [max(1, (n * sms) // self.n_ep) for n in sizes]
+            while sum(blocks) > sms and max(blocks) > 1:
+                k = max(range(n_parts), key=lambda i: blocks[i] / sizes[i] if blocks[i] > 1 else 0.0)
+                blocks[k] -= 1
+            while sum(blocks) < sms:
+                k = max(range(n_parts), key=lambda i: sizes[i] / blocks[i])
+                if sizes[k] / blocks[k] <= 1.0:
+                    break
+                blocks[k] += 1
+            blocks = [max(b, -(-n // tpb)) for b, n in zip(blocks, sizes)]   # never more than tpb episodes per CTA at once
+        else:
+            blocks = [min(sms, -(-n // tpb)) for n in sizes]
+        for (_m, a, b), nb in zip(self.parts, blocks):
+            p = ev.plan(b - a, want_placements, int(self.pods_per_ep[a:b].max()), tpb,
+                        episodes_per_policy=self.n_ep / self.n_structures, allow_dense=False)
+            p.blocks = int(nb)
+            p.scratch_bytes = nat.KS_SCRATCH_HEADER + p.scratch_per_team * p.blocks * p.teams_per_block
+            self.plans.append(p)
 
 
 class ResidentBatch:
