@@ -9,16 +9,32 @@
 // KS_PF_DBL(u64)->double, KS_PF_I2D(int)->double, KS_PF_FN (function qualifiers) and the tables of
 // ks_glibc_pow_tables.inc.
 //
-// Domain of the fast path (everything a scheduling policy produces): x positive and normal, 2^-65 <= |y| < 2^63,
-// and |y * log(x)| in [2^-54, 512).  Outside it *ok is cleared and the caller falls back.
+// Domain: x positive and finite (subnormals included), y finite and non-zero.  The function returns exactly what glibc
+// returns -- including its shortcuts for |y| < 2^-65 (1.0), |y| >= 2^63 and |y log x| >= 1024 (overflow to +inf, which
+// CPython turns into OverflowError, or underflow to 0.0) and |y log x| < 2^-54 (1.0) -- except in the band
+// 512 <= |y log x| < 1024 (results beyond 2^+-738), where glibc takes extra care of subnormal results that is not
+// ported: there *ok is cleared and the caller reports the operation as outside the translated subset.
 KS_PF_FN double ks_glibc_pow_fast(double x, double y, int* ok) {
   typedef unsigned long long u64;
-  const u64 ix = KS_PF_BITS(x), iy = KS_PF_BITS(y);
-  const unsigned topx = (unsigned)(ix >> 52), topy = (unsigned)(iy >> 52);
+  u64 ix = KS_PF_BITS(x);
+  const u64 iy = KS_PF_BITS(y);
+  unsigned topx = (unsigned)(ix >> 52);
+  const unsigned topy = (unsigned)(iy >> 52);
   *ok = 1;
-  if (topx - 1u > 0x7fdu || (topy & 0x7ffu) - 0x3beu > 0x7fu) {
-    *ok = 0;
-    return 0.0;
+  if ((topy & 0x7ffu) - 0x3beu > 0x7fu) {  // |y| < 2^-65 or |y| >= 2^63 (e_pow.c: "Special cases" for finite non-zero y)
+    if (ix == 0x3ff0000000000000ull) return 1.0;
+    if ((topy & 0x7ffu) < 0x3beu) return 1.0;  // 1.0 + y or 1.0 - y, which round to 1.0
+    return ((ix > 0x3ff0000000000000ull) == (topy < 0x800u)) ? KS_PF_DBL(0x7ff0000000000000ull) : 0.0;
+  }
+  if (topx - 1u > 0x7fdu) {
+    if (topx != 0u || ix == 0ull) {  // zero, negative, inf, nan: the callers handle these before calling
+      *ok = 0;
+      return 0.0;
+    }
+    // subnormal x: normalise (e_pow.c: ix = asuint64(x * 0x1p52); ix &= 0x7fff...; ix -= 52ULL << 52)
+    ix = KS_PF_BITS(KS_PF_MUL(x, 4503599627370496.0)) & 0x7fffffffffffffffull;
+    ix -= 52ull << 52;
+    topx = (unsigned)(ix >> 52);
   }
   // ---- log_inline ----
   const u64 tmp = ix - 0x3fe6955500000000ull;
@@ -53,7 +69,9 @@ KS_PF_FN double ks_glibc_pow_fast(double x, double y, int* ok) {
   // ---- exp_inline ----
   const unsigned abstop = (unsigned)(KS_PF_BITS(ehi) >> 52) & 0x7ffu;
   if (abstop - 0x3c9u > 0x3eu) {
-    *ok = 0;
+    if (abstop < 0x3c9u) return 1.0;  // |y log x| < 2^-54: 1.0 + ehi rounds to 1.0
+    if (abstop >= 0x409u) return (KS_PF_BITS(ehi) >> 63) ? 0.0 : KS_PF_DBL(0x7ff0000000000000ull);  // >= 1024: underflow / overflow
+    *ok = 0;  // 512 <= |y log x| < 1024: glibc's specialcase() path, not ported
     return 0.0;
   }
   double kd2 = KS_PF_FMA(ehi, KS_EXP_INVLN2N, KS_EXP_SHIFT);

@@ -35,9 +35,6 @@ __device__ __forceinline__ void ks_fail(int* st, int code) {
 extern "C" __device__ double ks_rt_pow(double x, double y);
 extern "C" __device__ double ks_rt_exp(double x);
 extern "C" __device__ double ks_rt_log(double x);
-extern "C" __device__ double ks_rt_sin(double x);
-extern "C" __device__ double ks_rt_cos(double x);
-extern "C" __device__ double ks_rt_tan(double x);
 extern "C" __device__ ks_int ks_rt_idiv(ks_int a, ks_int b);  // C truncating quotient, b != 0
 // `return max(lo, int(score))` as the scheduler wrapper sees it: int(max(0, .)) or the exception channel
 extern "C" __device__ long long ks_rt_ret_max_f2i(double score, long long lo, int st);
@@ -193,6 +190,54 @@ KS_D ks_int ks_fround(double x, int* st) {
   }
   return (ks_int)r;
 }
+// round(x, ndigits) for float x: CPython (Objects/floatobject.c double_round) prints x with ndigits decimals correctly
+// rounded (half to even on the EXACT binary value) and reads the decimal string back, i.e. the result is the double
+// nearest to R / 10^ndigits where R = round_half_even(x * 10^ndigits) computed without error.  Here: x = m * 2^e exactly,
+// m * 10^ndigits in 128 bits, shifted right by -e with the tie rule; R / 10^ndigits is one correctly rounded IEEE
+// division because both are exact doubles (R < 2^53, ndigits <= 15).  Outside that range: 'unsupported', never a guess.
+KS_D double ks_fround_n(double x, ks_int nd, int* st) {
+  if (isnan(x) || isinf(x) || x == 0.0) return x;
+  if (nd < 0 || nd > 15) { ks_fail(st, 2); return 0.0; }
+  const double ax = fabs(x);
+  if (ax >= 4503599627370496.0) return x;  // 2^52: already an integer
+  const ks_u64 bits = (ks_u64)__double_as_longlong(ax);
+  int e = (int)(bits >> 52);
+  ks_u64 m = bits & 0xfffffffffffffull;
+  if (e == 0) e = 1; else m |= 1ull << 52;
+  e -= 1075;  // ax = m * 2^e, e < 0 here
+  ks_u64 p10 = 1;
+  for (ks_int k = 0; k < nd; ++k) p10 *= 10ull;  // <= 10^15 < 2^50
+  const ks_u64 lo = m * p10, hi = __umul64hi(m, p10);  // m * 10^nd < 2^103
+  const int sh = -e;  // 1 .. 1074: R = (m * 10^nd) >> sh, rounded half to even on the bits shifted out
+  ks_u64 q = 0, rem_hi = 0, rem_lo = 0, half_hi = 1, half_lo = 0;  // defaults: remainder 0 < half -> rounds down to q
+  if (sh > 103) {
+    q = 0;  // the product is below 2^103 <= 2^(sh-1): less than one half, rounds to zero
+  } else if (sh < 64) {
+    if (hi >> sh) { ks_fail(st, 2); return 0.0; }  // R would not fit 64 bits
+    q = (lo >> sh) | (hi << (64 - sh));  // sh >= 1, so the left shift is by at most 63
+    rem_lo = lo & ((1ull << sh) - 1ull);
+    half_hi = 0;
+    half_lo = 1ull << (sh - 1);
+  } else if (sh == 64) {
+    q = hi;
+    rem_lo = lo;
+    half_hi = 0;
+    half_lo = 1ull << 63;
+  } else {
+    const int s2 = sh - 64;  // 1 .. 39
+    q = hi >> s2;
+    rem_hi = hi & ((1ull << s2) - 1ull);
+    rem_lo = lo;
+    half_hi = 1ull << (s2 - 1);
+    half_lo = 0;
+  }
+  const bool above = rem_hi > half_hi || (rem_hi == half_hi && rem_lo > half_lo);
+  const bool tie = rem_hi == half_hi && rem_lo == half_lo;
+  if (above || (tie && (q & 1ull))) q += 1;
+  if (q >= (1ull << 53)) { ks_fail(st, 2); return 0.0; }
+  const double r = ks_div((double)q, (double)p10);
+  return x < 0.0 ? -r : r;
+}
 KS_D double ks_msqrt(double x, int* st) {
   if (x < 0.0) { ks_fail(st, 1); return 0.0; }  // ValueError: math domain error
   return __dsqrt_rn(x);
@@ -208,18 +253,16 @@ KS_D double ks_mexp(double x, int* st) {
   if (isinf(r) && !isinf(x)) { ks_fail(st, 1); return 0.0; }  // OverflowError: math range error
   return r;
 }
+// math.sin / cos / tan: CPython returns glibc's results, which are not correctly rounded, and this runtime has no
+// operation-for-operation port of them (as it has for pow, exp and log).  A last-place difference can flip int(score),
+// so under the bit-exact contract they are outside the translated subset (status 'unsupported'), never approximated.
+// The domain error is still an exception: math.sin(inf) raises ValueError whatever the library.
 KS_D double ks_msin(double x, int* st) {
-  if (isinf(x)) { ks_fail(st, 1); return 0.0; }
-  return ks_rt_sin(x);
+  ks_fail(st, isinf(x) ? 1 : 2);
+  return 0.0;
 }
-KS_D double ks_mcos(double x, int* st) {
-  if (isinf(x)) { ks_fail(st, 1); return 0.0; }
-  return ks_rt_cos(x);
-}
-KS_D double ks_mtan(double x, int* st) {
-  if (isinf(x)) { ks_fail(st, 1); return 0.0; }
-  return ks_rt_tan(x);
-}
+KS_D double ks_mcos(double x, int* st) { return ks_msin(x, st); }
+KS_D double ks_mtan(double x, int* st) { return ks_msin(x, st); }
 KS_D double ks_mpow(double x, double y, int* st) { return ks_untag(ks_rt_mpow(x, y), st); }
 
 // ------------------------------------------------------------------------------- exact int <-> float order

@@ -32,12 +32,12 @@ import hashlib
 from dataclasses import dataclass, field
 from typing import Dict, List, Optional, Tuple
 
-INT, FLOAT, BOOL, NUM, GPU, GPULIST, ILIST, FLIST, STATIC, POD, NODE, NONE, GPUS, LAMBDA, MODULE, STR = (
+INT, FLOAT, BOOL, NUM, GPU, GPULIST, ILIST, FLIST, STATIC, POD, NODE, NONE, GPUS, LAMBDA, MODULE, STR, ELIST = (
     "int", "float", "bool", "num", "gpu", "gpulist", "ilist", "flist", "static", "pod", "node", "none", "gpus",
-    "lambda", "module", "str")
+    "lambda", "module", "str", "elist")   # elist: `xs = []` whose element type the .append() calls decide
 NUMERIC = (INT, FLOAT, BOOL, NUM)
 CTYPE = {INT: "ks_int", FLOAT: "double", BOOL: "int", NUM: "KsNum", GPU: "int", GPULIST: "KsGpuList",
-         ILIST: "KsIntList", FLIST: "KsFloatList"}
+         ILIST: "KsIntList", FLIST: "KsFloatList", ELIST: "KsIntList"}
 
 ALLOWED_BUILTINS = {"abs", "min", "max", "sum", "len", "range", "enumerate", "int", "float", "bool", "str", "round",
                     "sorted"}
@@ -103,6 +103,8 @@ class CompiledPolicy:
 def _join(a: Optional[str], b: str) -> str:
     if a is None or a == b:
         return b
+    if ELIST in (a, b) and {a, b} <= {ELIST, GPULIST, ILIST, FLIST}:
+        return b if a == ELIST else a
     s = {a, b}
     if s <= {INT, BOOL}:
         return INT
@@ -123,6 +125,17 @@ def _flit(x: float) -> str:
 
 class _Returned(Exception):
     pass
+
+
+def _def_as_lambda(fn: ast.FunctionDef) -> Optional[ast.Lambda]:
+    """A helper `def f(a, b): [docstring] return <expr>` is the lambda `lambda a, b: <expr>` (inlined at its call sites
+    like any lambda); anything longer is not translated."""
+    body = [st for st in fn.body if not (isinstance(st, ast.Expr) and isinstance(st.value, ast.Constant))]
+    a = fn.args
+    if len(body) != 1 or not isinstance(body[0], ast.Return) or body[0].value is None or fn.decorator_list or a.vararg or a.kwarg \
+            or a.kwonlyargs or a.defaults or a.posonlyargs:
+        return None
+    return ast.copy_location(ast.Lambda(args=a, body=body[0].value), fn)
 
 
 class _Translator:
@@ -151,11 +164,16 @@ class _Translator:
         self.static_vars: Dict[str, Val] = {}
         self.defined: set = set()
         self.uses_budget = False
+        self.try_labels: List[str] = []         # handler labels of the enclosing try bodies
+        self.ntry = 0
         args = [a.arg for a in fn.args.args]
         if len(args) != 2 or fn.args.vararg or fn.args.kwarg or fn.args.kwonlyargs or fn.args.defaults:
             raise PolicyCompileError("priority_function must take exactly (pod, node)")
         self.pod_name, self.node_name = args
         self.assign_count: Dict[str, int] = {}
+        # names that are built up with .append(): `xs = []` then `xs.append(v)` in loops / branches
+        self.appended = {n.func.value.id for n in ast.walk(fn) if isinstance(n, ast.Call) and isinstance(n.func, ast.Attribute)
+                         and n.func.attr == "append" and isinstance(n.func.value, ast.Name)}
         for n in ast.walk(fn):
             if isinstance(n, (ast.Assign, ast.AugAssign, ast.AnnAssign)):
                 tg = n.targets if isinstance(n, ast.Assign) else [n.target]
@@ -167,6 +185,8 @@ class _Translator:
                 for nm in ast.walk(n.target):
                     if isinstance(nm, ast.Name):
                         self.assign_count[nm.id] = self.assign_count.get(nm.id, 0) + 2
+            elif isinstance(n, ast.FunctionDef) and n is not fn:
+                self.assign_count[n.name] = self.assign_count.get(n.name, 0) + 1
 
     # ------------------------------------------------------------------ emission helpers
     def emit(self, s: str):
@@ -181,15 +201,23 @@ class _Translator:
         self.emit(f"const {CTYPE[ty]} {name} = {expr};")
         return Val(ty, name, bits=bits, const=const)
 
+    def exc(self) -> str:
+        """The statement that raises: leave the function, or -- inside a try body -- jump to the handler."""
+        if self.try_labels:
+            return f"{{ if (!st) st = 1; goto {self.try_labels[-1]}; }}"
+        return "KS_RETURN(KS_RET_EXCEPTION);"
+
     def raise_exc(self):
-        self.emit("KS_RETURN(KS_RET_EXCEPTION);")
+        self.emit(self.exc())
 
     def unsupported_rt(self):
         self.emit("KS_RETURN(KS_RET_UNSUPPORTED);")
 
     def check_st(self):
-        # the status word is sticky (ks_pyrt.cuh): it is tested where the function returns
-        pass
+        # The status word is sticky (ks_pyrt.cuh): outside a try body it is tested where the function returns.  Inside
+        # one, control must reach the handler before anything after the failing operation takes effect.
+        if self.try_labels:
+            self.emit(f"if (st) goto {self.try_labels[-1]};")
 
     def fail(self, node, msg):
         line = getattr(node, "lineno", "?")
@@ -288,9 +316,11 @@ class _Translator:
             if name not in self.defined:
                 self.need_flag.add(name)
                 if name in self.flagged:
-                    self.emit(f"if (!b_{name}) KS_RETURN(KS_RET_EXCEPTION);  // UnboundLocalError")
+                    self.emit(f"if (!b_{name}) {self.exc()}  // UnboundLocalError")
             return Val(ty, f"v_{name}", bits=self.var_bits.get(name, 64))
         if name in self.consts:
+            if isinstance(self.consts[name], ast.Lambda):
+                return Val(LAMBDA, node=self.consts[name])
             return self.const_val(self.consts[name], node)
         if name == "math" or name == "operator":
             return Val(MODULE, name)
@@ -320,6 +350,22 @@ class _Translator:
         self.fail(node, f"constant of type {type(c).__name__}")
 
     def store(self, name: str, v: Val, node, additive: bool = False):
+        if v.ty == STATIC and not v.items and name in self.appended and not self.scopes:
+            # `xs = []` of a list that .append() fills: a real (bounded) list variable; its element type comes from the
+            # appends (found by the type-inference iteration), the assignment itself just empties it
+            prev = self.seen_types.get(name)
+            self.seen_types[name] = _join(prev, ELIST)
+            ty = self.var_types.get(name)
+            if ty is None:
+                ty = self.var_types[name] = ELIST
+            if ty not in (ELIST, GPULIST, ILIST, FLIST):
+                self.fail(node, f"variable {name!r} holds both a list and {ty}")
+            if ty != ELIST:
+                self.emit(f"v_{name}.n = 0;")
+            if name in self.flagged:
+                self.emit(f"b_{name} = 1;")
+            self.defined.add(name)
+            return
         if v.ty in (STATIC, LAMBDA, NONE, STR, POD, NODE, GPUS, MODULE):
             if v.ty == GPUS:
                 v = self.gpus_to_list()
@@ -448,7 +494,7 @@ class _Translator:
             self.check_st()
             return v
         if isinstance(op, ast.Div):
-            self.emit(f"if ({b.code} == 0) KS_RETURN(KS_RET_EXCEPTION);  // ZeroDivisionError")
+            self.emit(f"if ({b.code} == 0) {self.exc()}  // ZeroDivisionError")
             if a.bits <= 53 and b.bits <= 53:
                 return self.tmp(FLOAT, f"ks_div((double){a.code}, (double){b.code})")
             v = self.tmp(FLOAT, f"ks_itruediv({a.code}, {b.code}, &st)")
@@ -709,7 +755,7 @@ class _Translator:
                 bits = max(args[0].bits, args[1].bits)
             if len(args) == 3:
                 step = args[2].code
-                self.emit(f"if ({step} == 0) KS_RETURN(KS_RET_EXCEPTION);  // ValueError: range() arg 3 must not be zero")
+                self.emit(f"if ({step} == 0) {self.exc()}  // ValueError: range() arg 3 must not be zero")
             i = self.new("i")
             self.uses_budget = True
             self.emit("#pragma unroll 1")
@@ -1022,13 +1068,15 @@ class _Translator:
         if "res" not in state:
             self.raise_exc()  # empty literal: ValueError
             raise _Returned()
-        self.emit(f"if (!{found}) KS_RETURN(KS_RET_EXCEPTION);  // ValueError: empty sequence")
+        self.emit(f"if (!{found}) {self.exc()}  // ValueError: empty sequence")
         return Val(state["ety"], state["res"], bits=state["bits"] if state["ety"] in (INT, BOOL) else 64)
 
     def apply_lambda(self, fn_node: ast.AST, args: List[Val], node) -> Val:
         lam = fn_node
         if isinstance(fn_node, ast.Name) and fn_node.id in self.static_vars and self.static_vars[fn_node.id].ty == LAMBDA:
             lam = self.static_vars[fn_node.id].node
+        elif isinstance(fn_node, ast.Name) and not self.shadowed(fn_node.id) and isinstance(self.consts.get(fn_node.id), ast.Lambda):
+            lam = self.consts[fn_node.id]
         if not isinstance(lam, ast.Lambda):
             self.fail(node, "only lambda expressions can be used as key functions")
         params = [a.arg for a in lam.args.args]
@@ -1125,7 +1173,7 @@ class _Translator:
                 and len(c.args) == 2 and isinstance(c.args[0], ast.Constant) and type(c.args[0].value) is int
                 and abs(c.args[0].value) < 2 ** 62 and isinstance(c.args[1], ast.Call)
                 and isinstance(c.args[1].func, ast.Name) and c.args[1].func.id == "int" and not c.args[1].keywords
-                and len(c.args[1].args) == 1 and not self.shadowed("max") and not self.shadowed("int")):
+                and len(c.args[1].args) == 1 and not self.shadowed("max") and not self.shadowed("int")) or self.try_labels:
             return False
         saved = (list(self.lines), self.ind, self.ntmp, dict(self.seen_types), dict(self.seen_bits), set(self.need_flag),
                  dict(self.var_types), dict(self.var_bits), set(self.defined), dict(self.static_vars))
@@ -1155,6 +1203,9 @@ class _Translator:
         if isinstance(f, ast.Attribute) and isinstance(f.value, ast.Name) and f.value.id in ("math", "operator") \
                 and not self.shadowed(f.value.id):
             return self.call_module(f.value.id, f.attr, node)
+        if isinstance(f, ast.Attribute) and f.attr == "append" and isinstance(f.value, ast.Name) and f.value.id in self.appended \
+                and f.value.id in self.assign_count and not self.scopes:
+            return self.list_append(f.value.id, node)
         if isinstance(f, ast.Attribute):
             self.fail(node, f"method call .{f.attr}()")
         if isinstance(f, ast.Lambda):
@@ -1164,6 +1215,10 @@ class _Translator:
         name = f.id
         if name in self.static_vars and self.static_vars[name].ty == LAMBDA:
             return self.apply_lambda(f, [self.expr(a) for a in node.args], node)
+        if not self.shadowed(name) and isinstance(self.consts.get(name), ast.Lambda):
+            if node.keywords:
+                self.fail(node, "keyword arguments to a helper function")
+            return self.apply_lambda(self.consts[name], [self.expr(a) for a in node.args], node)
         if self.shadowed(name):
             self.fail(node, f"call of local name {name!r}")
         if name not in ALLOWED_BUILTINS:
@@ -1271,8 +1326,47 @@ class _Translator:
                     return r
                 self.raise_exc()
                 raise _Returned()
-            self.fail(node, "round(x, ndigits) needs decimal-correct rounding and is not supported")
+            if len(args) == 2 and args[1].ty in (INT, BOOL):
+                v, nd = args[0], self.as_int(args[1])
+                if v.ty in (INT, BOOL):
+                    if nd.const is not None and int(nd.const) >= 0:
+                        return self.as_int(v)      # round(int, n >= 0) is the int itself
+                    self.fail(node, "round(int, negative or dynamic ndigits)")
+                if v.ty == FLOAT:
+                    if nd.const is not None and not 0 <= int(nd.const) <= 15:
+                        self.fail(node, "round(x, ndigits) with ndigits outside 0..15")
+                    r = self.tmp(FLOAT, f"ks_fround_n({v.code}, {nd.code}, &st)")   # a float, not an int, in CPython too
+                    self.check_st()
+                    return r
+                self.fail(node, "round(x, ndigits) of a dynamically typed number")
+            self.raise_exc()   # TypeError: ndigits must be an integer
+            raise _Returned()
         self.fail(node, f"builtin {name}()")
+
+    def list_append(self, name: str, node: ast.Call) -> Val:
+        """xs.append(v) on a local list that started as `xs = []` (bounded: KS_LIST_CAP elements, 8 for GPU lists)."""
+        if len(node.args) != 1 or node.keywords:
+            self.raise_exc()  # TypeError: append() takes exactly one argument
+            raise _Returned()
+        cur = self.lookup(name, node)            # UnboundLocalError when appended to before `xs = []`
+        v = self.expr(node.args[0])
+        want = {INT: ILIST, BOOL: ILIST, FLOAT: FLIST, GPU: GPULIST}.get(v.ty)
+        if want is None:
+            self.fail(node, f"append of a {v.ty} value")
+        if cur.ty not in (ELIST, want):
+            self.fail(node, f"list {name!r} holds elements of more than one type")
+        self.seen_types[name] = _join(self.seen_types.get(name), want)
+        self.var_types[name] = _join(self.var_types.get(name), want)
+        if cur.ty == ELIST:
+            return Val(NONE)   # element type learnt in this pass; the next pass emits the code
+        cap = "KS_MAX_GPUS_PER_NODE" if want == GPULIST else "KS_LIST_CAP"
+        self.emit(f"if (v_{name}.n >= {cap}) KS_RETURN(KS_RET_UNSUPPORTED);")
+        if want == GPULIST:
+            self.emit(f"v_{name}.g[v_{name}.n++] = (signed char){v.code};")
+        else:
+            code = v.code if want == FLIST else self.as_int(v).code
+            self.emit(f"v_{name}.v[v_{name}.n++] = {code};")
+        return Val(NONE)
 
     def call_module(self, mod: str, attr: str, node: ast.Call) -> Val:
         if node.keywords:
@@ -1362,7 +1456,7 @@ class _Translator:
                 self.emit(f"switch ({k.code}) {{")
                 for j, it in enumerate(base.items):
                     self.emit(f"  case {j}: {res} = {self.convert(it, rty)}; break;")
-                self.emit("  default: KS_RETURN(KS_RET_EXCEPTION);  // IndexError")
+                self.emit(f"  default: {self.exc()}  // IndexError")
                 self.emit("}")
                 return Val(rty, res, bits=max(it.bits for it in base.items) if rty in (INT, BOOL) else 64)
             k = int(idx.const)
@@ -1379,7 +1473,7 @@ class _Translator:
             raise _Returned()
         k = self.new("j")
         self.emit(f"ks_int {k} = {idx.code}; if ({k} < 0) {k} += {n};")
-        self.emit(f"if ({k} < 0 || {k} >= {n}) KS_RETURN(KS_RET_EXCEPTION);  // IndexError")
+        self.emit(f"if ({k} < 0 || {k} >= {n}) {self.exc()}  // IndexError")
         if base.ty == GPUS:
             # "& 7" is the identity on a checked index; it keeps the shared-memory load in range when the compiler
             # hoists it (ks_ns is a plain, non-volatile ld.shared) above the IndexError test
@@ -1485,6 +1579,8 @@ class _Translator:
             if self.return_max_int_of_float(s.value):
                 return False
             v = self.expr(s.value)
+            # (the scheduler's wrapper int(max(0, .)) runs in the caller, outside any try of the policy: what it raises
+            # -- int(inf) -- is not catchable by the policy, so ks_wrap_* may return the exception code directly)
             if v.ty in (INT, BOOL):
                 self.emit(f"KS_RETURN(ks_wrap_i({self.as_int(v).code}));")
             elif v.ty == FLOAT:
@@ -1492,7 +1588,7 @@ class _Translator:
             elif v.ty == NUM:
                 self.emit(f"KS_RETURN(ks_wrap_n({v.code}));")
             else:
-                self.raise_exc()  # max(0, <list/None/...>): TypeError
+                self.emit("KS_RETURN(KS_RET_EXCEPTION);")  # max(0, <list/None/...>) in the wrapper: TypeError, not catchable
             return False
         if isinstance(s, ast.Assign):
             v = self.expr(s.value)
@@ -1599,6 +1695,14 @@ class _Translator:
             self.emit("}")
             self.defined = before
             return True
+        if isinstance(s, ast.FunctionDef):
+            lam = _def_as_lambda(s)
+            if lam is None:
+                self.fail(s, f"helper function {s.name!r} is more than a single return statement")
+            self.store(s.name, Val(LAMBDA, node=lam), s)
+            return True
+        if isinstance(s, ast.Try):
+            return self.try_stmt(s, loop_depth)
         if isinstance(s, ast.Break):
             self.emit("break;")
             return False
@@ -1609,12 +1713,75 @@ class _Translator:
             self.fail(s, "import")
         if isinstance(s, ast.Assert):
             c = self.expr(s.test)
-            self.emit(f"if (!{self.truth(c)}) KS_RETURN(KS_RET_EXCEPTION);  // AssertionError")
+            self.emit(f"if (!{self.truth(c)}) {self.exc()}  // AssertionError")
             return True
         if isinstance(s, ast.Raise):
             self.raise_exc()
             return False
         self.fail(s, f"statement {type(s).__name__}")
+
+    def try_stmt(self, s: ast.Try, loop_depth: int) -> bool:
+        """try / except / else.  In the reference's sandbox only a bare `except:` can catch anything: the restricted
+        builtins (safe_execution.py:98-124) hold no exception classes, so `except ZeroDivisionError:` raises NameError
+        while the exception is being matched, and that NameError leaves the try statement (later clauses are not tried).
+        A try body therefore either has a bare first handler, which catches everything the policy can raise, or a first
+        handler that turns any exception into another exception -- i.e. no handler at all."""
+        if s.finalbody:
+            self.fail(s, "try ... finally is not supported")
+        bare = bool(s.handlers) and s.handlers[0].type is None
+        if not bare:
+            # no effective handler: the body runs as if it were not wrapped (else: follows on normal completion)
+            falls = self.block(s.body, loop_depth)
+            if falls and s.orelse:
+                falls = self.block(s.orelse, loop_depth)
+            return falls
+        self.ntry += 1
+        k = self.ntry
+        label, done, flag = f"ks_try{k}", f"ks_try{k}_ok", f"tr{k}"
+        before = set(self.defined)
+        self.emit(f"int {flag} = 0;")
+        self.emit("{")
+        self.ind += 1
+        self.try_labels.append(label)
+        try:
+            body_falls = self.block(s.body, loop_depth)
+        finally:
+            self.try_labels.pop()
+        after_body = set(self.defined)
+        self.ind -= 1
+        self.emit("}")
+        self.emit(f"goto {done};")
+        self.emit(f"{label}: {flag} = 1;")
+        self.emit(f"{done}:;")
+        self.emit(f"if ({flag}) {{")
+        self.ind += 1
+        # leaving the translated subset is not an exception the policy could have caught
+        self.emit("if (st != 1) KS_RETURN(KS_RET_UNSUPPORTED);")
+        self.emit("st = 0;")
+        self.defined = set(before)   # the body may have stopped anywhere
+        h = s.handlers[0]
+        if h.name:
+            self.fail(s, "except ... as name")
+        h_falls = self.block(h.body, loop_depth)
+        after_h = set(self.defined)
+        self.ind -= 1
+        if s.orelse or True:
+            self.emit("} else {")
+            self.ind += 1
+            self.defined = set(after_body)
+            e_falls = self.block(s.orelse, loop_depth) if (s.orelse and body_falls) else body_falls
+            after_e = set(self.defined)
+            self.ind -= 1
+        self.emit("}")
+        if h_falls and e_falls:
+            self.defined = after_h & after_e
+        elif h_falls:
+            self.defined = after_h
+        elif e_falls:
+            self.defined = after_e
+        else:
+            return False
+        return True
 
     def run(self) -> bool:
         return self.block(self.fn.body[self.skip:])
@@ -1634,7 +1801,19 @@ def _module_constants(tree: ast.Module, fn: ast.FunctionDef) -> Dict[str, object
             except Exception:  # noqa: BLE001
                 pass
         if isinstance(s, ast.FunctionDef):
-            raise PolicyCompileError(f"line {s.lineno}: helper function {s.name!r} is not supported")
+            lam = _def_as_lambda(s)
+            if lam is None:
+                raise PolicyCompileError(f"line {s.lineno}: helper function {s.name!r} is more than a single return statement")
+            # inlined at the call site, where names resolve in priority_function's scope: the helper may only read its
+            # own parameters, module-level constants and builtins
+            params = {a.arg for a in s.args.args}
+            local_names = {n.id for n in ast.walk(fn) if isinstance(n, ast.Name) and isinstance(n.ctx, ast.Store)} | \
+                          {a.arg for a in fn.args.args}
+            free = {n.id for n in ast.walk(lam.body) if isinstance(n, ast.Name)} - params
+            if free & local_names:
+                raise PolicyCompileError(f"line {s.lineno}: helper {s.name!r} reads a name that is local to priority_function")
+            consts[s.name] = lam
+            continue
         raise PolicyCompileError(f"line {getattr(s, 'lineno', '?')}: unsupported module-level statement")
     return consts
 
@@ -1783,9 +1962,9 @@ def compile_policy(source: str) -> CompiledPolicy:
         raise PolicyCompileError("no priority_function defined")
     fn = fns[-1]
     for n in ast.walk(fn):
-        if isinstance(n, (ast.FunctionDef, ast.AsyncFunctionDef, ast.ClassDef)) and n is not fn:
-            raise PolicyCompileError(f"line {n.lineno}: nested definitions are not supported")
-        if isinstance(n, (ast.Try, ast.With, ast.Global, ast.Nonlocal, ast.Yield, ast.YieldFrom, ast.Await, ast.Delete,
+        if isinstance(n, (ast.AsyncFunctionDef, ast.ClassDef)):
+            raise PolicyCompileError(f"line {n.lineno}: nested class / async definitions are not supported")
+        if isinstance(n, (ast.With, ast.Global, ast.Nonlocal, ast.Yield, ast.YieldFrom, ast.Await, ast.Delete,
                           ast.NamedExpr, ast.JoinedStr, ast.Dict, ast.Set, ast.DictComp, ast.SetComp, ast.Starred)):
             raise PolicyCompileError(f"line {getattr(n, 'lineno', '?')}: {type(n).__name__} is not supported")
     consts = _module_constants(tree, fn)
@@ -1827,6 +2006,8 @@ def compile_policy(source: str) -> CompiledPolicy:
         body.append(f"  int budget = {LOOP_BUDGET};")
     for name in sorted(tr.var_types):
         ty = tr.var_types[name]
+        if ty == ELIST:
+            ty = ILIST   # never appended to on any path the translator saw: an empty list of whatever
         init = {INT: "0", FLOAT: "0.0", BOOL: "0", NUM: "ks_num_i(0)", GPU: "0"}.get(ty)
         if init is None:
             body.append(f"  {CTYPE[ty]} v_{name}; v_{name}.n = 0;")

@@ -154,8 +154,19 @@ class Gen:
                 self.lists.append(name)
                 return s
             return f"{pad}pass\n"
-        if k < 0.95:
+        if k < 0.93:
             return f"{pad}for i in range({r.choice(['3', 'pod.num_gpu', 'len(node.gpus)', '1, 4'])}):\n{pad}    score = score + i * {self.expr(2)}\n"
+        if k < 0.97 and d < 2:
+            # try / except: only a bare handler catches in the reference's sandbox (its builtins hold no exception classes)
+            vars_before = list(self.vars)
+            s = f"{pad}try:\n" + self.block(ind + 1, d + 1)
+            if r.random() < 0.5:
+                s += f"{pad}    score = score + node.gpus[{r.choice(['0', '5', 'pod.num_gpu'])}].gpu_milli_left / {r.choice(['pod.num_gpu', '(node.gpu_left - 1)', '2'])}\n"
+            s += f"{pad}except{r.choice(['', '', '', ' ZeroDivisionError', ' Exception'])}:\n" + self.block(ind + 1, d + 1)
+            if r.random() < 0.3:
+                s += f"{pad}else:\n" + self.block(ind + 1, d + 1)
+            self.vars = vars_before
+            return s
         return f"{pad}return {self.expr(0)}\n"
 
     def block(self, ind, d):

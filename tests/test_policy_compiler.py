@@ -89,16 +89,33 @@ def test_template_prefix_is_hoisted_only_when_it_is_exactly_the_template():
 @pytest.mark.parametrize("body", [
     "import os\n    return 1",
     "node.cpu_milli_left = 0\n    return 1",
-    "try:\n        return 1\n    except:\n        return 2",
-    "return round(pod.cpu_milli / 3, 2)",
+    "try:\n        return 1\n    finally:\n        pass",
+    "return round(pod.cpu_milli / 3, -2)",
     "return len(str(pod.cpu_milli))",
-    "def helper(x):\n        return x\n    return helper(1)",
+    "def helper(x):\n        y = x\n        return y\n    return helper(1)",
     "d = {}\n    return 1",
 ])
 def test_unsupported_constructs_are_refused(body):
     from funsearch_kubernetes_simulator_b200.policy_compiler import PolicyCompileError, compile_policy
     with pytest.raises(PolicyCompileError):
         compile_policy("def priority_function(pod, node):\n    " + body + "\n")
+
+
+def test_widened_constructs_translate():
+    """try / bare except / else, single-return helper functions (nested and module level), round(x, n), lists built with
+    .append(): translated, not refused."""
+    from funsearch_kubernetes_simulator_b200.policy_compiler import compile_policy
+    t = compile_policy("def priority_function(pod, node):\n    try:\n        s = 1 / pod.num_gpu\n    except:\n        s = 2.5\n"
+                       "    else:\n        s += 1\n    return s\n").cuda_source
+    assert "goto ks_try1" in t and "st = 0;" in t
+    # a named exception class does not exist in the sandbox: the clause raises NameError while matching, nothing is caught
+    t = compile_policy("def priority_function(pod, node):\n    try:\n        s = 1 / pod.num_gpu\n    except ZeroDivisionError:\n        s = 2.5\n    return s\n").cuda_source
+    assert "goto" not in t
+    t = compile_policy("W = 3\ndef f(a):\n    return a * W\ndef priority_function(pod, node):\n    def g(b):\n        return b + 1\n    return g(f(pod.num_gpu))\n").cuda_source
+    assert "3LL" in t
+    assert "ks_fround_n" in compile_policy("def priority_function(pod, node):\n    return round(node.gpu_left / 3, 2)\n").cuda_source
+    cp = compile_policy("def priority_function(pod, node):\n    xs = []\n    for g in node.gpus:\n        xs.append(g.gpu_milli_left * 0.5)\n    return sum(xs)\n")
+    assert cp.var_types["xs"] == "flist"
 
 
 def test_runtime_errors_become_exception_returns():
