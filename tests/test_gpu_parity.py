@@ -439,7 +439,7 @@ def test_device_pow_is_bit_identical_to_host_libm(env):
     # the one band that is not ported is declined (a tagged NaN -> status 'unsupported'), never approximated
     declined = (got.view(np.uint64) >> np.uint64(32)) == np.uint64(0x7ff8dead)
     band = np.abs(y * np.log(x))
-    assert ((band[declined] > 500) & (band[declined] < 1030)).all() and declined.sum() < 0.02 * len(x)
+    assert ((band[declined] > 500) & (band[declined] < 1030)).all() and 0 < declined.sum() <= m and not declined[:n].any()
     bad = np.nonzero((got.view(np.uint64) != want.view(np.uint64)) & ~declined)[0]
     assert bad.size == 0, f"{bad.size} of {len(x)} differ, e.g. x={x[bad[0]]!r} y={y[bad[0]]!r} got={got[bad[0]]!r} want={want[bad[0]]!r}"
 
