@@ -1739,6 +1739,10 @@ class _Translator:
         k = self.ntry
         label, done, flag = f"ks_try{k}", f"ks_try{k}_ok", f"tr{k}"
         before = set(self.defined)
+        if not self.try_labels:
+            # outside a try body failures are sticky and only tested at the return: one that happened BEFORE this try
+            # statement must not be mistaken for one of its body's (the handler would swallow it)
+            self.emit("if (st) KS_RETURN(0);")
         self.emit(f"int {flag} = 0;")
         self.emit("{")
         self.ind += 1

@@ -78,6 +78,9 @@ TRICKY = [
     "def priority_function(pod, node):\n    s = sum(1 / 0 for g in node.gpus)\n    return 5 + s\n",
     "def priority_function(pod, node):\n    t = sorted(node.gpus, key=lambda g: undefined_name)\n    return 9 + len(t)\n",
     "def priority_function(pod, node):\n    for g in node.gpus:\n        return nothing\n    return 11\n",
+    # a failure before a try statement is not the try body's: the handler must not swallow it (found by the fuzz)
+    "def priority_function(pod, node):\n    t = 0.0 or (3 // (pod.memory_mib % pod.cpu_milli))\n    try:\n        s = 1 / pod.num_gpu\n    except:\n        s = 2\n    return int(s + t)\n",
+    "def priority_function(pod, node):\n    s = 0\n    try:\n        s = node.gpus[pod.num_gpu].gpu_milli_left // pod.num_gpu\n    except:\n        s = 5\n    else:\n        s += 100 // (node.gpu_left - 1)\n    return s + 1\n",
     # Python number semantics
     "def priority_function(pod, node):\n    return (-7 // 2) * -100 + (-7 % 3) * 10 + int(-7.5 % 2 * 2) + (7 // -2) * -1000\n",
     "def priority_function(pod, node):\n    return max(1, 1.0) + min(2.0, 2) + round(2.5) + round(3.5) + int(-0.9) + abs(-3) + (True + True)\n",
