@@ -113,6 +113,66 @@ def test_population_sample_against_oracle(env):
         assert abs(out.policy_score - ref.score) <= 1e-9 * max(abs(ref.score), 1e-300), k
 
 
+def test_bench_population_on_the_full_trace_against_oracle(env):
+    """The workload bench.py measures (configs[1]): the first 64 policies of the benchmarked generation on the FULL default
+    trace, every counter, the placement log and all metrics against the oracle."""
+    from helpers import oracle_specs, outcome_digest
+    from oracle import pysim
+    from funsearch_kubernetes_simulator_b200.variants import policy_population
+    cluster = env["ClusterSpec"].load("gpu16")
+    tr = env["Trace"].load("default")
+    pop = policy_population(1024, seed=0)[:64]
+    ev = env["BatchEvaluator"](cluster, [tr])
+    compiled = ev.compile(pop)
+    assert all(c is not None for c in compiled)
+    outs = ev.run_episodes(compiled, list(range(64)), [0] * 64, want_placements=True)
+    cs, ts = oracle_specs(cluster, tr)
+    declined = 0
+    for k, (src, out) in enumerate(zip(pop, outs)):
+        ref = pysim.run_episode(cs, ts, pysim.scorer_from_source(src))
+        if out.status == 4:          # left the translated subset (e.g. a complex intermediate): reported, never a number
+            declined += 1
+            assert ref.status != 0 or out.policy_score == 0.0, k
+            continue
+        assert (out.status, out.events, out.attempts, out.placed) == (ref.status, ref.events, ref.attempts, ref.placed), k
+        if ref.status != 0:
+            assert out.policy_score == 0.0, k
+            continue
+        assert (out.max_nodes, out.max_waiting, out.last_event_time) == (ref.max_nodes, ref.max_waiting, ref.last_event_time), k
+        assert outcome_digest(tr, cluster, out) == pysim.placement_digest(ts, cs, ref), k
+        r = out.results
+        assert (r.num_snapshots, r.num_fragmentation_events) == (ref.num_snapshots, ref.num_fragmentation_events), k
+        for got, want in ((r.avg_cpu_utilization, ref.avg_cpu), (r.avg_memory_utilization, ref.avg_mem),
+                          (r.avg_gpu_count_utilization, ref.avg_gpu_count), (r.avg_gpu_memory_utilization, ref.avg_gpu_milli),
+                          (r.gpu_fragmentation_score, ref.fragmentation), (out.policy_score, ref.score)):
+            assert abs(got - want) <= 1e-9 * max(abs(want), 1e-300), (k, got, want)
+    assert declined <= 3
+
+
+def test_bootstrap_seeds_on_full_traces_against_oracle(env):
+    """configs[3]'s "seeds": bootstrap resamples 1-3 of two FULL bundled traces (one pre-sorted, one not) under three
+    policies, against the oracle."""
+    from helpers import oracle_specs, outcome_digest
+    from oracle import pysim
+    from funsearch_kubernetes_simulator_b200.workload import bootstrap_trace
+    cluster = env["ClusterSpec"].load("gpu16")
+    traces = [bootstrap_trace(env["Trace"].load(nm), s) for nm in ("default", "cpu200") for s in (1, 2, 3)]
+    pn = ["ts_best_fit", "ts_funsearch_4816", "fs_utilization_based"]
+    ev = env["BatchEvaluator"](cluster, traces)
+    compiled = ev.compile([env["pol"][p] for p in pn])
+    ep_pol = [p for p in range(3) for _t in range(6)]
+    ep_tr = [t for _p in range(3) for t in range(6)]
+    outs = ev.run_episodes(compiled, ep_pol, ep_tr, want_placements=True)
+    for e, out in enumerate(outs):
+        tr = traces[ep_tr[e]]
+        cs, ts = oracle_specs(cluster, tr)
+        ref = pysim.run_episode(cs, ts, pysim.scorer_from_source(env["pol"][pn[ep_pol[e]]]))
+        assert (out.status, out.events, out.attempts, out.placed) == (ref.status, ref.events, ref.attempts, ref.placed), e
+        assert (out.max_nodes, out.max_waiting, out.last_event_time) == (ref.max_nodes, ref.max_waiting, ref.last_event_time), e
+        assert outcome_digest(tr, cluster, out) == pysim.placement_digest(ts, cs, ref), e
+        assert abs(out.policy_score - ref.score) <= 1e-9 * max(abs(ref.score), 1e-300), e
+
+
 def test_policy_major_table_and_two_ctas_per_sm(env):
     """A trace-major episode table is replayed policy-major (same-policy episodes side by side on an SM) and, being
     several waves long with many episodes per policy, by the two-CTAs-per-SM kernel; results come back in the caller's
@@ -299,6 +359,8 @@ def _compare_with_c_oracle(tag, cluster, trace, out, builtin, params=None):
     import numpy as np
     assert np.array_equal(out.final_creation_time, t) and np.array_equal(out.node_index, n) and np.array_equal(out.gpu_mask, m), tag
     for got, want in ((out.policy_score, res.score), (out.results.avg_cpu_utilization, res.avg_cpu),
+                      (out.results.avg_memory_utilization, res.avg_mem), (out.results.avg_gpu_count_utilization, res.avg_gpu_count),
+                      (out.results.avg_gpu_memory_utilization, res.avg_gpu_milli),
                       (out.results.gpu_fragmentation_score, res.fragmentation)):
         assert abs(got - want) <= 1e-9 * max(abs(want), 1e-300), (tag, got, want)
 
