@@ -11,11 +11,14 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libks_b200.so")
+# KS_B200_LIB selects another build of the library (e.g. libks_b200_invariants.so, the debug variant of build.py)
+LIB_PATH = os.environ.get("KS_B200_LIB") or os.path.join(_HERE, "libks_b200.so")
 
 # status words (include/ks_abi.h)
-ST_OK, ST_POLICY_EXCEPTION, ST_GPU_SHORTFALL, ST_STEP_BUDGET, ST_UNSUPPORTED, ST_CAPACITY = range(6)
-STATUS_NAMES = {0: "ok", 1: "policy_exception", 2: "gpu_shortfall", 3: "step_budget", 4: "unsupported", 5: "capacity"}
+ST_OK, ST_POLICY_EXCEPTION, ST_GPU_SHORTFALL, ST_STEP_BUDGET, ST_UNSUPPORTED, ST_CAPACITY, ST_INVARIANT = range(7)
+STATUS_NAMES = {0: "ok", 1: "policy_exception", 2: "gpu_shortfall", 3: "step_budget", 4: "unsupported", 5: "capacity",
+                6: "invariant_violated"}
+BUILD_PHASE_CLOCKS, BUILD_INVARIANTS = 1, 2
 
 KS_POD_INTS = 8
 KS_NC_FIELDS = 20
@@ -80,6 +83,7 @@ _SIGNATURES = {
     "ks_last_error": (C.c_char_p, []),
     "ks_compile_log": (C.c_char_p, []),
     "ks_api_version": (C.c_int, []),
+    "ks_build_flags": (C.c_int, []),
     "ks_init": (C.c_int, [C.c_int]),
     "ks_trace_pack": (C.c_int, [C.c_longlong] + [C.c_void_p] * 10),
     "ks_cluster_pack": (C.c_int, [C.c_int] + [C.c_void_p] * 7),

@@ -56,6 +56,7 @@ class EpisodeOutcome:
     node_index: Optional[np.ndarray] = None   # -1 = never placed
     gpu_mask: Optional[np.ndarray] = None
     waiting: Optional[np.ndarray] = None      # bool: member of waiting_pods when the replay ended (main.py:116-117)
+    invariant_check: int = 0                  # debug build, status 6: (failing check << 32) | node index
 
     @property
     def status_name(self) -> str:
@@ -536,6 +537,8 @@ class BatchEvaluator:
             oc = EpisodeOutcome(int(r["status"]), float(r["policy_score"]), results, int(r["events"]), int(r["attempts"]),
                                 int(r["scorer_calls"]), int(r["placed"]), int(r["max_nodes"]), int(r["max_waiting"]),
                                 int(r["last_event_time"]), int(r["device_cycles"]))
+            if oc.status == nat.ST_INVARIANT:
+                oc.invariant_check = int(r["reserved"][0])
             if want_placements:
                 tr = self.traces[int(ep_trace[e])]
                 rank = tr.packed()[0]

@@ -4,9 +4,11 @@
   KubernetesSimulator(cluster, pod_list, ...).run_schedule() mutating Pod.assigned_node /
   assigned_gpus / creation_time in place (simulator/main.py:28-72, 126-138) and exposing max_nodes and
   get_evaluation_results().
-* `check_invariants` is the host-side counterpart of validate_invariants=True
-  (simulator/main.py:201-272): it replays the placement log and checks that no node or GPU was ever
-  over-committed and that the accounting returns to the totals.
+* validate_invariants=True (simulator/main.py:201-272) has two counterparts: with the debug build of the library
+  (build.py --invariants, selected by KS_B200_LIB) the KERNEL runs the reference's checks on its live state after every
+  mutation and ends the episode on the first violation; with the production build `check_invariants` replays the
+  placement log on the host and checks that no node or GPU was ever over-committed and that the accounting returns to
+  the totals.
 """
 from __future__ import annotations
 
@@ -34,6 +36,24 @@ def write_back(outcome: EpisodeOutcome, pods: List, cluster: ClusterSpec) -> Non
         else:
             pod.assigned_node = ""
             pod.assigned_gpus = []
+
+
+INVARIANT_MESSAGES = {
+    1: "has negative CPU remaining", 2: "has negative memory remaining", 3: "has negative GPU count remaining",
+    4: "CPU remaining exceeds total", 5: "memory remaining exceeds total", 6: "GPU remaining exceeds total",
+    7: "has a GPU with negative milli remaining", 8: "has a GPU whose milli remaining exceeds total",
+    9: "CPU accounting error", 10: "memory accounting error", 11: "GPU accounting error", 12: "GPU milli accounting error"}
+
+
+def write_back_cluster(outcome: EpisodeOutcome, cluster_obj) -> None:
+    """Node / GPU `*_left` after a completed replay (simulator/main.py:83-96, 126-128): every placed pod has also been
+    deleted by the time the event heap is empty, so every resource is back at its total."""
+    for node in cluster_obj.nodes_dict.values():
+        node.cpu_milli_left = node.cpu_milli_total
+        node.memory_mib_left = node.memory_mib_total
+        node.gpu_left = len(node.gpus)
+        for g in node.gpus:
+            g.gpu_milli_left = g.gpu_milli_total
 
 
 def check_invariants(outcome: EpisodeOutcome, cluster: ClusterSpec, trace: Trace) -> None:
@@ -98,6 +118,7 @@ class GpuKubernetesSimulator:
         self.trace = Trace.from_pods(pod_list)
         self._ev = evaluator or BatchEvaluator(self.cluster, [self.trace], device)
         self.max_nodes = 0
+        self.waiting_pods: List = []     # pods that failed at least once and were never placed (main.py:42, 116-117)
         self.outcome: Optional[EpisodeOutcome] = None
 
     def run_schedule(self) -> None:
@@ -109,11 +130,16 @@ class GpuKubernetesSimulator:
             raise RuntimeError("the policy raised during the replay (the reference's worker would score it 0)")
         if self.outcome.status == 2:
             raise ValueError("Not enough GPUs available on the chosen node")   # simulator/main.py:164-165
+        if self.outcome.status == 6:   # debug build of the library: the kernel's own _validate_cluster_invariants failed
+            code, node = self.outcome.invariant_check >> 32, self.outcome.invariant_check & 0xFFFFFFFF
+            raise ValueError(f"Node {self.cluster.node_ids[node]} {INVARIANT_MESSAGES.get(code, 'violates an invariant')}")
         if self.outcome.status != 0:
             raise RuntimeError(f"episode ended with status {self.outcome.status_name}")
         write_back(self.outcome, self.pod_list, self.cluster)
+        write_back_cluster(self.outcome, self.cluster_obj)
+        self.waiting_pods = [p for p, w in zip(self.pod_list, self.outcome.waiting) if w]
         self.max_nodes = self.outcome.max_nodes
-        if self.validate_invariants:
+        if self.validate_invariants and not (self._ev.lib.ks_build_flags() & 2):
             check_invariants(self.outcome, self.cluster, self.trace)
 
     def get_evaluation_results(self) -> Optional[EvaluationResults]:

@@ -137,6 +137,13 @@ class ClusterSpec:
         for i, nd in enumerate(nodes):
             if len(nd.gpus) > 8:
                 raise ValueError(f"node {nd.node_id} has {len(nd.gpus)} GPUs; at most 8 are supported")
+            # The replay starts every episode from a pristine copy of the cluster (what the reference's callers pass:
+            # a deepcopy of the parsed cluster, funsearch_integration.py:46-48).  A cluster that is already partly
+            # used, or whose gpu_left disagrees with its GPU list, would be replayed differently by the reference.
+            if getattr(nd, "gpu_left", len(nd.gpus)) != len(nd.gpus) or nd.cpu_milli_left != nd.cpu_milli_total \
+                    or nd.memory_mib_left != nd.memory_mib_total or any(g.gpu_milli_left != g.gpu_milli_total for g in nd.gpus):
+                raise ValueError(f"node {nd.node_id} is not pristine (its *_left fields differ from its totals, or gpu_left "
+                                 "from len(gpus)): pass the cluster as parsed, before any replay")
             for j, g in enumerate(nd.gpus):
                 gmil[i, j] = g.gpu_milli_total
                 gmem[i, j] = g.memory_mib_total

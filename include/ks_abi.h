@@ -14,6 +14,8 @@
 #define KS_ST_STEP_BUDGET 3       // caller-supplied event budget exhausted (the reference has none)
 #define KS_ST_UNSUPPORTED 4       // policy left the supported subset at run time (int64 overflow, complex ...)
 #define KS_ST_CAPACITY 5          // a per-slot scratch capacity was exceeded
+#define KS_ST_INVARIANT 6         // debug build only: _validate_cluster_invariants failed (simulator/main.py:201-272);
+                                  // KsResult.reserved[0] = (number of the failing check << 32) | node index
 
 // ---- what a policy function returns instead of a score when it cannot -----------------
 // Scores handed to the simulator are int(max(0, score)) >= 0 (funsearch_integration.py:96),

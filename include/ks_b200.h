@@ -28,6 +28,11 @@ const char* ks_last_error(void);
 
 int ks_api_version(void);
 
+/* Build variant of the loaded library: bit 0 = diagnostic phase clocks, bit 1 = KS_DEBUG_INVARIANTS (the kernel runs
+ * _validate_cluster_invariants, simulator/main.py:201-272, after every mutation and ends the episode with status
+ * KS_ST_INVARIANT on the first violation -- the counterpart of KubernetesSimulator(..., validate_invariants=True)). */
+int ks_build_flags(void);
+
 /* Bind the calling thread to `device` (its primary context, shared with torch) and load the CUDA
  * driver.  Fails loudly when no driver / no sm_100 device is present: there is no CPU fallback.
  * Replaces nothing in the reference (it has no device); precondition of everything below. */

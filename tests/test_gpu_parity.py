@@ -458,6 +458,82 @@ def test_object_protocol_facade(env):
     g = env["gold"]["runs"]["edge:test_simulator|sim_int_best_fit"]
     assert abs(sim.get_policy_score() - float.fromhex(g["score"])) < 1e-12 and sim.max_nodes == g["max_nodes"]
     assert sim.get_evaluation_results().num_snapshots == g["num_snapshots"]
+    # the rest of the object protocol: nothing is left waiting, every resource is back at its total (main.py:83-96)
+    assert sim.waiting_pods == [] and (node1.cpu_milli_left, node1.gpu_left, node1.gpus[1].gpu_milli_left) == (8000, 2, 1000)
+    # an oversized pod with no deletion pending is dropped and stays in waiting_pods (SURVEY App. A.9 case 1)
+    big = NS(pod_id="pod9", cpu_milli=99000, memory_mib=1, num_gpu=0, gpu_milli=0, gpu_spec="", creation_time=1,
+             duration_time=5, assigned_node="", assigned_gpus=[])
+    pods2 = [NS(**vars(p)) for p in pods[:1]] + [big]
+    for p in pods2:
+        p.assigned_node, p.assigned_gpus = "", []
+    pods2[0].creation_time = 50
+    sim2 = GpuKubernetesSimulator(cluster, pods2, env["pol"]["sim_int_best_fit"])
+    sim2.run_schedule()
+    assert sim2.waiting_pods == [big] and big.assigned_node == "" and pods2[0].assigned_node == "node2"
+    assert sim2.get_policy_score() == 0.0
+    node1.cpu_milli_left -= 1
+    with pytest.raises(ValueError, match="not pristine"):
+        GpuKubernetesSimulator(cluster, pods, env["pol"]["sim_int_best_fit"])
+    node1.cpu_milli_left += 1
+
+
+def test_device_side_invariant_checks_in_the_debug_build(env):
+    """validate_invariants=True on the device: the debug build of the library (build.py --invariants) runs the reference's
+    _validate_cluster_invariants (main.py:201-272) on the kernel's live state after every mutation.  A policy that ignores
+    capacity drives a node negative and the episode stops there with the reference's message; well-behaved policies
+    replay exactly as in the production build.  Run in a subprocess: the library variant is chosen at import time."""
+    import os
+    import subprocess
+    import sys
+    from funsearch_kubernetes_simulator_b200 import build
+    lib = build.build(invariants=True)
+    script = r'''
+import json, sys
+from types import SimpleNamespace as NS
+sys.path.insert(0, "tests")
+from helpers import load_golden
+from funsearch_kubernetes_simulator_b200 import ClusterSpec, Trace, _native as nat
+from funsearch_kubernetes_simulator_b200.evaluator import BatchEvaluator
+from funsearch_kubernetes_simulator_b200.integration import GpuKubernetesSimulator
+assert nat.lib().ks_build_flags() & 2
+gold, pol = load_golden()
+c, t = ClusterSpec.load("gpu16"), Trace.load("default").head(3000)
+def objects():
+    nodes = {}
+    for i, nid in enumerate(c.node_ids):
+        gpus = [NS(memory_mib_left=int(c.gpu_mem_total[i, g]), memory_mib_total=int(c.gpu_mem_total[i, g]),
+                   gpu_milli_left=int(c.gpu_milli_total[i, g]), gpu_milli_total=int(c.gpu_milli_total[i, g])) for g in range(int(c.num_gpus[i]))]
+        nodes[nid] = NS(node_id=nid, cpu_milli_left=int(c.cpu_total[i]), cpu_milli_total=int(c.cpu_total[i]),
+                        memory_mib_left=int(c.mem_total[i]), memory_mib_total=int(c.mem_total[i]), gpu_left=len(gpus), gpus=gpus)
+    pods = [NS(pod_id=t.pod_ids[i], cpu_milli=int(t.cpu_milli[i]), memory_mib=int(t.memory_mib[i]), num_gpu=int(t.num_gpu[i]),
+               gpu_milli=int(t.gpu_milli[i]), gpu_spec="", creation_time=int(t.creation_time[i]), duration_time=int(t.duration_time[i]),
+               assigned_node="", assigned_gpus=[]) for i in range(t.n_pods)]
+    return NS(nodes_dict=nodes), pods
+out = {}
+cl, pods = objects()
+try:
+    GpuKubernetesSimulator(cl, pods, pol["x_ignores_capacity"], validate_invariants=True).run_schedule()
+    out["bad"] = "no error"
+except ValueError as e:
+    out["bad"] = str(e)
+cl, pods = objects()
+sim = GpuKubernetesSimulator(cl, pods, pol["ts_funsearch_4816"], validate_invariants=True)
+sim.run_schedule()
+out["good"] = [sim.outcome.events, sim.outcome.placed, sim.get_policy_score().hex()]
+print("RESULT " + json.dumps(out))
+'''
+    root = os.path.abspath(os.path.join(os.path.dirname(__file__), ".."))
+    r = subprocess.run([sys.executable, "-c", script], cwd=root, env=dict(os.environ, KS_B200_LIB=lib, PYTHONPATH=root),
+                       capture_output=True, text=True, timeout=900)
+    assert r.returncode == 0, r.stderr[-3000:]
+    import json
+    out = json.loads([ln for ln in r.stdout.splitlines() if ln.startswith("RESULT ")][-1][7:])
+    assert "has negative CPU remaining" in out["bad"] or "has negative memory remaining" in out["bad"], out["bad"]
+    # the same episode in the production build of this process
+    cluster, tr = env["ClusterSpec"].load("gpu16"), env["Trace"].load("default").head(3000)
+    ev = env["BatchEvaluator"](cluster, [tr])
+    o = ev.run_episodes(ev.compile([env["pol"]["ts_funsearch_4816"]]), [0], [0])[0]
+    assert out["good"] == [o.events, o.placed, o.policy_score.hex()]
 
 
 def test_device_pow_is_bit_identical_to_host_libm(env):
