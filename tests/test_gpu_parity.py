@@ -509,10 +509,23 @@ def objects():
                gpu_milli=int(t.gpu_milli[i]), gpu_spec="", creation_time=int(t.creation_time[i]), duration_time=int(t.duration_time[i]),
                assigned_node="", assigned_gpus=[]) for i in range(t.n_pods)]
     return NS(nodes_dict=nodes), pods
+IGNORES_CPU_AND_MEMORY = """
+def priority_function(pod, node):
+    if pod.num_gpu > node.gpu_left:
+        return 0
+    if pod.num_gpu > 0:
+        n = 0
+        for g in node.gpus:
+            if g.gpu_milli_left >= pod.gpu_milli:
+                n += 1
+        if n < pod.num_gpu:
+            return 0
+    return 1000 - len(node.gpus)
+"""
 out = {}
 cl, pods = objects()
 try:
-    GpuKubernetesSimulator(cl, pods, pol["x_ignores_capacity"], validate_invariants=True).run_schedule()
+    GpuKubernetesSimulator(cl, pods, IGNORES_CPU_AND_MEMORY, validate_invariants=True).run_schedule()
     out["bad"] = "no error"
 except ValueError as e:
     out["bad"] = str(e)
@@ -529,6 +542,7 @@ print("RESULT " + json.dumps(out))
     import json
     out = json.loads([ln for ln in r.stdout.splitlines() if ln.startswith("RESULT ")][-1][7:])
     assert "has negative CPU remaining" in out["bad"] or "has negative memory remaining" in out["bad"], out["bad"]
+    assert out["bad"].startswith("Node openb-node-")
     # the same episode in the production build of this process
     cluster, tr = env["ClusterSpec"].load("gpu16"), env["Trace"].load("default").head(3000)
     ev = env["BatchEvaluator"](cluster, [tr])
