@@ -11,7 +11,10 @@ reps = int(sys.argv[2]) if len(sys.argv) > 2 else 3
 pop = policy_population(n, seed=0)
 ev = BatchEvaluator(ClusterSpec.load("gpu16"), [Trace.load("default")])
 compiled = ev.compile(pop)
+ev.bind(compiled)
+ev.wait_background()   # the generation's structures relinked into one module: the steady state bench.py times
 rb = ev.prepare_resident(compiled, list(range(n)), [0] * n)
+print("modules in batch", rb.n_modules, "structures", rb.n_structures, flush=True)
 for it in range(reps):
     e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
     e0.record(); rb.launch(); e1.record(); torch.cuda.synchronize()
