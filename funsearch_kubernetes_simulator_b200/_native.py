@@ -54,7 +54,7 @@ class KsPlan(C.Structure):
 
 class KsBatch(C.Structure):
     _fields_ = [("traces", C.c_void_p), ("ep_policy", C.c_void_p), ("ep_const", C.c_void_p), ("consts", C.c_void_p),
-                ("ep_trace", C.c_void_p), ("nconst", C.c_void_p),
+                ("ep_trace", C.c_void_p), ("range_begin", C.c_void_p), ("nconst", C.c_void_p),
                 ("results", C.c_void_p), ("placements", C.c_void_p), ("place_off", C.c_void_p), ("scratch", C.c_void_p),
                 ("totals", C.c_longlong * 4), ("max_events", C.c_longlong), ("snapshot_interval", C.c_double)]
 
@@ -66,7 +66,7 @@ class KsHostTrace(C.Structure):
 class KsHostBatch(C.Structure):
     _fields_ = [("traces", C.POINTER(KsHostTrace)), ("n_traces", C.c_int), ("reserved", C.c_int),
                 ("ep_policy", C.c_void_p), ("ep_const", C.c_void_p), ("consts", C.c_void_p), ("n_consts", C.c_longlong),
-                ("ep_trace", C.c_void_p), ("nconst", C.c_void_p), ("results", C.c_void_p),
+                ("ep_trace", C.c_void_p), ("range_begin", C.c_void_p), ("nconst", C.c_void_p), ("results", C.c_void_p),
                 ("placements", C.c_void_p), ("place_off", C.c_void_p), ("placements_len", C.c_longlong),
                 ("totals", C.c_longlong * 4), ("max_events", C.c_longlong), ("snapshot_interval", C.c_double)]
 

@@ -176,6 +176,7 @@ class BatchEvaluator:
         self.warps_per_team = 0   # 0 = planner's choice; set to force a team width
         self.ctas_per_sm = 0      # 0 = planner's choice; 1 = latency kernel, 2 = dense (throughput) kernel
         self.module_structures = 0  # test knob: at most this many structures per linked module (0 = no limit)
+        self.pack_by_cost = True    # single-wave batches: cut the table into per-SM ranges by predicted cost
         # Compile workers are started now, not inside the first evaluation: they warm up (imports, libnvrtc) while the
         # caller is still generating its first population.
         if processes is None:
@@ -573,17 +574,21 @@ class BatchEvaluator:
 
     # ------------------------------------------------------------------ resident form (inputs already in HBM)
     def prepare_resident(self, policies: Sequence[CompiledPolicy], ep_policy: Sequence[int], ep_trace: Sequence[int],
-                         teams_per_block: int = 0, single_module: Optional[bool] = None, max_events: int = 0) -> "ResidentBatch":
+                         teams_per_block: int = 0, single_module: Optional[bool] = None, max_events: int = 0,
+                         costs=None) -> "ResidentBatch":
+        """`costs` (optional, one per episode): predicted relative cost, e.g. device cycles or events of an earlier replay
+        of the same or the parent policy; single-wave batches are packed onto the SMs by it (_pack_single_wave)."""
         return ResidentBatch(self, policies, ep_policy, ep_trace, teams_per_block, single_module=single_module,
-                             max_events=max_events)
+                             max_events=max_events, costs=costs)
 
     # ------------------------------------------------------------------ host-buffer (end-to-end) form
     def prepare_host_batch(self, policies: Sequence[CompiledPolicy], ep_policy: Sequence[int], ep_trace: Sequence[int],
-                           teams_per_block: int = 0, single_module: Optional[bool] = None, max_events: int = 0) -> "HostBatch":
+                           teams_per_block: int = 0, single_module: Optional[bool] = None, max_events: int = 0,
+                           costs=None) -> "HostBatch":
         """Stage a batch in pinned host memory for ks_eval_batch_host (everything the step needs crosses
         PCIe inside the call: traces, cluster table, episode table in; results out)."""
         return HostBatch(self, policies, ep_policy, ep_trace, teams_per_block, single_module=single_module,
-                         max_events=max_events)
+                         max_events=max_events, costs=costs)
 
     # ------------------------------------------------------------------ reference-shaped entry points
     def evaluate_population(self, codes: Sequence[str], trace_ids: Optional[Sequence[int]] = None,
@@ -689,7 +694,7 @@ class _Tables:
     module.  Shared by the resident and the host-buffer batch."""
 
     def __init__(self, ev: BatchEvaluator, policies, ep_policy, ep_trace, teams_per_block, want_placements, pin,
-                 single_module):
+                 single_module, costs=None):
         ep_policy = np.ascontiguousarray(ep_policy, dtype=np.int64)
         ep_trace = np.ascontiguousarray(ep_trace, dtype=np.int32)
         self.n_ep = len(ep_policy)
@@ -711,6 +716,17 @@ class _Tables:
             self.inverse = np.argsort(self.order)
         else:
             self.ep_slot, self.ep_const = np.ascontiguousarray(self.ep_slot), np.ascontiguousarray(self.ep_const)
+        # predicted cost of each episode (sorted order): the caller's (e.g. cycles or events of an earlier replay, of the
+        # parent policy), else a proxy: size of the policy's code x pods of the trace
+        if costs is not None:
+            cost = np.asarray(costs, dtype=np.float64)
+            if cost.shape != (self.n_ep,):
+                raise ValueError("one cost per episode")
+        else:
+            size = np.array([len(p.cuda_source) for p in policies], dtype=np.float64)
+            cost = size[ep_policy] * np.array([ev.traces[t].n_pods for t in ep_trace], dtype=np.float64)
+        self.cost = cost if self.order is None else cost[self.order]
+        self.range_begin = None
         self.n_structures = int(len(np.unique(part.astype(np.int64) * nat.KS_MAX_TABLE + self.ep_slot)))
         self.pods_per_ep = np.array([ev.traces[t].n_pods for t in self.ep_trace], dtype=np.int64)
         # one part per module: [start, end) of the sorted table
@@ -723,8 +739,12 @@ class _Tables:
         n_parts = len(self.parts)
         self.plans = []
         if n_parts == 1:
-            self.plans.append(ev.plan(self.n_ep, want_placements, int(self.pods_per_ep.max()), teams_per_block,
-                                      episodes_per_policy=self.n_ep / self.n_structures))
+            p = ev.plan(self.n_ep, want_placements, int(self.pods_per_ep.max()), teams_per_block,
+                        episodes_per_policy=self.n_ep / self.n_structures)
+            self.plans.append(p)
+            if p.warps_per_team == 1 and p.ctas_per_sm == 1 and teams_per_block == 0 and ev.sm_count < self.n_ep <= 8 * ev.sm_count \
+                    and not want_placements and ev.pack_by_cost:
+                self._pack_single_wave(ev, want_placements)
             return
         whole = ev.plan(self.n_ep, False, 1, teams_per_block, allow_dense=False)
         tpb = whole.teams_per_block
@@ -751,15 +771,60 @@ class _Tables:
             self.plans.append(p)
 
 
+def _pack_single_wave(self, ev, want_placements):
+    """A generation that fits the GPU in one wave is as long as its slowest episode, and an episode is slower the more
+    CODE its SM has to keep in the instruction cache (profiles/README.md).  The table is therefore cut into one explicit
+    range per SM by LPT on the predicted cost: episodes in order of decreasing cost, each to the SM with the smallest
+    load so far, at most 8 per SM; the kernel replays exactly these ranges (no stealing).  Measured on configs[1]
+    (tools/pack_probe.py): with the default cost -- the size of the policy's code, which needs no earlier measurement --
+    116.7 -> 106.9 ms; cycles or events measured by an earlier replay are worse predictors (111 / 117 ms), and giving
+    the heaviest episodes SMs of their own is worse than the default cut (146 ms).  Result order is restored by the
+    callers through `order` / `inverse` as before."""
+    import heapq
+    n, sms = self.n_ep, ev.sm_count
+    by = np.argsort(-self.cost, kind="stable")
+    # LPT with at most 8 per SM: the heaviest episode left goes to the SM with the smallest predicted load so far
+    heap = [(0.0, k) for k in range(sms)]
+    bins = [[] for _ in range(sms)]
+    for e in by:
+        while True:
+            load, k = heapq.heappop(heap)
+            if len(bins[k]) < 8:
+                break
+        bins[k].append(int(e))
+        if len(bins[k]) < 8:
+            heapq.heappush(heap, (load + float(self.cost[e]), k))
+    bins = [bn for bn in bins if bn]
+    sizes = [len(bn) for bn in bins]
+    by_cost = np.array([e for bn in bins for e in bn], dtype=np.int64)
+    c = self.cost[by_cost]
+    hi = max(sum(self.cost[e] for e in bn) for bn in bins) / max(float(self.cost.max()), 1e-30)
+    plan = ev.plan(n, want_placements, int(self.pods_per_ep.max()), 8, episodes_per_policy=1.0, allow_dense=False)
+    plan.blocks = len(sizes)
+    plan.scratch_bytes = nat.KS_SCRATCH_HEADER + plan.scratch_per_team * plan.blocks * plan.teams_per_block
+    self.plans = [plan]
+    self.range_begin = np.concatenate([[0], np.cumsum(sizes)]).astype(np.int32)
+    # the table in packed order
+    self.ep_slot, self.ep_const, self.ep_trace = (np.ascontiguousarray(a[by_cost]) for a in (self.ep_slot, self.ep_const, self.ep_trace))
+    self.pods_per_ep = self.pods_per_ep[by_cost]
+    self.cost = self.cost[by_cost]
+    self.order = by_cost if self.order is None else self.order[by_cost]
+    self.inverse = np.argsort(self.order)
+    self.predicted_makespan_over_heaviest = hi
+
+
+_Tables._pack_single_wave = _pack_single_wave
+
+
 class ResidentBatch:
     """A batch whose episode table, result buffer and scratch already live in HBM: launch() is one ks_eval_batch call
     (one memset + one kernel) per module the batch's structures live in, all in flight together, nothing else."""
 
     def __init__(self, ev: BatchEvaluator, policies, ep_policy, ep_trace, teams_per_block=0, want_placements=False,
-                 max_events=0, pin=True, single_module=None):
+                 max_events=0, pin=True, single_module=None, costs=None):
         torch = ev._torch
         self.ev = ev
-        t = self.tables = _Tables(ev, policies, ep_policy, ep_trace, teams_per_block, want_placements, pin, single_module)
+        t = self.tables = _Tables(ev, policies, ep_policy, ep_trace, teams_per_block, want_placements, pin, single_module, costs)
         self.n_ep = t.n_ep
         self.order = t.order
         self.n_structures = t.n_structures
@@ -777,6 +842,7 @@ class ResidentBatch:
             self.d_kf = torch.from_numpy(t.bound.consts).to(ev.device)
             self.d_tr = torch.from_numpy(t.ep_trace).to(ev.device)
             self.d_res = torch.zeros(self.n_ep * rec, dtype=torch.uint8, device=ev.device)
+            self.d_ranges = torch.from_numpy(t.range_begin).to(ev.device) if t.range_begin is not None else None
             self.d_place = self.d_off = None
             if want_placements:
                 padded = (t.pods_per_ep + 1) // 2 * 2
@@ -792,6 +858,7 @@ class ResidentBatch:
             kb.ep_const = self.d_cof.data_ptr() + 4 * a
             kb.consts = self.d_kf.data_ptr()
             kb.ep_trace = self.d_tr.data_ptr() + 4 * a
+            kb.range_begin = self.d_ranges.data_ptr() if self.d_ranges is not None else None
             kb.nconst = ev._nconst.data_ptr()
             kb.results = self.d_res.data_ptr() + rec * a
             kb.placements = self.d_place.data_ptr() if want_placements else None
@@ -863,10 +930,11 @@ class HostBatch:
     """One batch held in pinned host memory + device workspaces; run() = one ks_eval_batch_host call per module the
     batch's structures live in (concurrently, each on its own stream)."""
 
-    def __init__(self, ev: BatchEvaluator, policies, ep_policy, ep_trace, teams_per_block=0, single_module=None, max_events=0):
+    def __init__(self, ev: BatchEvaluator, policies, ep_policy, ep_trace, teams_per_block=0, single_module=None, max_events=0,
+                 costs=None):
         torch = ev._torch
         self.ev = ev
-        t = self.tables = _Tables(ev, policies, ep_policy, ep_trace, teams_per_block, False, True, single_module)
+        t = self.tables = _Tables(ev, policies, ep_policy, ep_trace, teams_per_block, False, True, single_module, costs)
         self.n_ep = t.n_ep
         self.order = t.order
         if t.order is not None:   # the table that crosses PCIe is sorted; run() undoes it
@@ -884,6 +952,7 @@ class HostBatch:
         self.h_cof = pinned(t.ep_const)
         self.h_kf = pinned(t.bound.consts)
         self.h_tr = pinned(t.ep_trace)
+        self.h_ranges = pinned(t.range_begin) if t.range_begin is not None else None
         self.h_res = torch.empty(self.n_ep * rec, dtype=torch.uint8).pin_memory()
         self.h_traces = (nat.KsHostTrace * len(ev.traces))()
         for i, tr in enumerate(ev.traces):
@@ -904,6 +973,7 @@ class HostBatch:
             hb.consts = self.h_kf.data_ptr()
             hb.n_consts = int(t.bound.consts.size)
             hb.ep_trace = self.h_tr.data_ptr() + 4 * a
+            hb.range_begin = self.h_ranges.data_ptr() if self.h_ranges is not None else None
             hb.nconst = self.h_nconst.data_ptr()
             hb.results = self.h_res.data_ptr() + rec * a
             hb.placements = None

@@ -130,6 +130,7 @@ struct KsLaunch {
   const int* ep_trace;   // [n_episodes]
   const int* nconst;     // [n_pad][KS_NC_FIELDS]
   int* work_counter;     // [gridDim.x] zeroed by the host before launch: next entry of each CTA's range of the table
+  const int* range_begin;  // optional [gridDim.x + 1]: explicit table ranges per CTA (cost-packed table, no stealing)
   KsResult* results;     // [n_episodes]
   unsigned long long* placements;  // optional; episode e writes [place_off[e], +n_pods)
   const long long* place_off;      // [n_episodes] or null

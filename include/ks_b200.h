@@ -136,6 +136,9 @@ typedef struct KsBatch {
   const int* ep_const;            /* device [n_episodes], optional: where the policy's float literals start in consts */
   const double* consts;           /* device, optional: the float literals of the batch's policies, back to back */
   const int* ep_trace;            /* device [n_episodes] */
+  const int* range_begin;         /* device [plan.blocks + 1], optional: CTA b replays table entries [range_begin[b],
+                                     range_begin[b + 1]) and nothing else (a table packed by predicted cost); null = the
+                                     kernel cuts the table into equal ranges and idle teams steal from other ranges */
   const int* nconst;              /* device: packed cluster (ks_cluster_pack) */
   KsResult* results;              /* device [n_episodes] */
   unsigned long long* placements; /* device, optional */
@@ -200,6 +203,7 @@ typedef struct KsHostBatch {
   const double* consts;           /* host [n_consts], optional */
   long long n_consts;
   const int* ep_trace;            /* host [n_episodes] */
+  const int* range_begin;         /* host [plan.blocks + 1], optional (see KsBatch) */
   const int* nconst;              /* host, from ks_cluster_pack */
   KsResult* results;              /* host [n_episodes], out */
   unsigned long long* placements; /* host, optional out: episode e at place_off[e] */
