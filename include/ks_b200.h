@@ -138,7 +138,8 @@ typedef struct KsBatch {
   const int* ep_trace;            /* device [n_episodes] */
   const int* range_begin;         /* device [plan.blocks + 1], optional: CTA b replays table entries [range_begin[b],
                                      range_begin[b + 1]) and nothing else (a table packed by predicted cost); null = the
-                                     kernel cuts the table into equal ranges and idle teams steal from other ranges */
+                                     kernel cuts the table into equal ranges and idle teams steal from other ranges.
+                                     Explicit ranges belong to one block count: do not edit plan.blocks with them */
   const int* nconst;              /* device: packed cluster (ks_cluster_pack) */
   KsResult* results;              /* device [n_episodes] */
   unsigned long long* placements; /* device, optional */
