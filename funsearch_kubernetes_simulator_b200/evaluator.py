@@ -129,7 +129,7 @@ class BatchEvaluator:
     POOL_STRUCTURES = 24        # new structures from which NVRTC + link in the pool pays off
     MAX_MODULES = 128           # loaded modules kept (least recently used ones are released)
     MAX_PARTS = 32              # modules one batch may be spread over; beyond, the smallest contributions are merged
-    CONSOLIDATE_PARTS = 6       # a batch spread over more modules than this is relinked into ONE module in the background
+    CONSOLIDATE_PARTS = 1       # a batch spread over more modules than this is relinked into ONE module in the background
 
     def __init__(self, cluster: ClusterSpec, traces: Sequence[Trace], device: int = 0,
                  snapshot_interval: float = 0.05, cache_dir: Optional[str] = None, processes: Optional[int] = None):
