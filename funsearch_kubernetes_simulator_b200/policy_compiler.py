@@ -173,7 +173,7 @@ class _Translator:
         self.assign_count: Dict[str, int] = {}
         # names that are built up with .append(): `xs = []` then `xs.append(v)` in loops / branches
         self.appended = {n.func.value.id for n in ast.walk(fn) if isinstance(n, ast.Call) and isinstance(n.func, ast.Attribute)
-                         and n.func.attr == "append" and isinstance(n.func.value, ast.Name)}
+                         and n.func.attr in ("append", "extend") and isinstance(n.func.value, ast.Name)}
         for n in ast.walk(fn):
             if isinstance(n, (ast.Assign, ast.AugAssign, ast.AnnAssign)):
                 tg = n.targets if isinstance(n, ast.Assign) else [n.target]
@@ -270,6 +270,14 @@ class _Translator:
         if ty == NUM:
             return self.as_num(v)
         raise PolicyCompileError(f"cannot store {v.ty} into a {ty} variable")
+
+    @staticmethod
+    def is_set(v: Val) -> bool:
+        return v.ty == STATIC and v.const == "<set>"
+
+    @staticmethod
+    def is_dict(v: Val) -> bool:
+        return v.ty == STATIC and isinstance(v.const, tuple) and len(v.const) == 2 and v.const[0] == "<dict>"
 
     def truth(self, v: Val) -> str:
         if v.ty == BOOL:
@@ -570,7 +578,12 @@ class _Translator:
             self.fail(node, "'is' between non-None values")
         if isinstance(op, (ast.In, ast.NotIn)):
             if b.ty != STATIC:
-                self.fail(node, "'in' is only supported against a literal list/tuple")
+                self.fail(node, "'in' is only supported against a literal list/tuple/set/dict")
+            if self.is_dict(b):
+                if a.const is None or a.ty not in (STR, INT):
+                    self.fail(node, "'in' on a dict with a non-constant key")
+                hit = a.const in b.const[1]
+                return ("1" if hit else "0") if isinstance(op, ast.In) else ("0" if hit else "1")
             parts = [self.compare_pair(ast.Eq(), a, it, node) for it in b.items]
             e = "(" + " || ".join(parts) + ")" if parts else "0"
             return e if isinstance(op, ast.In) else f"(!{e})"
@@ -788,6 +801,8 @@ class _Translator:
                 elem = self.tmp(INT if src.ty == ILIST else FLOAT, f"{src.code}.v[{i}]")
                 cnt = Val(INT, f"(ks_int){i}", bits=6)
             elif src.ty == STATIC:
+                if self.is_set(src) or self.is_dict(src):
+                    self.fail(node, "iteration over a set / dict literal")
                 # unrolled
                 for k, item in enumerate(src.items):
                     self.emit("{")
@@ -929,6 +944,8 @@ class _Translator:
             return
         src = self.expr(arg)
         if src.ty == STATIC:
+            if self.is_set(src) or self.is_dict(src):
+                self.fail(node, "iteration over a set / dict literal")
             for it in src.items:
                 fn(it)
             return
@@ -1206,6 +1223,13 @@ class _Translator:
         if isinstance(f, ast.Attribute) and f.attr == "append" and isinstance(f.value, ast.Name) and f.value.id in self.appended \
                 and f.value.id in self.assign_count and not self.scopes:
             return self.list_append(f.value.id, node)
+        if isinstance(f, ast.Attribute) and f.attr == "extend" and isinstance(f.value, ast.Name) and f.value.id in self.appended \
+                and f.value.id in self.assign_count and not self.scopes and len(node.args) == 1 and not node.keywords \
+                and isinstance(node.args[0], (ast.List, ast.Tuple)):
+            # xs.extend([a, b]) with a literal: the elements are evaluated first, then appended one by one
+            for el in node.args[0].elts:
+                self.list_append(f.value.id, ast.copy_location(ast.Call(func=f, args=[el], keywords=[]), node))
+            return Val(NONE)
         if isinstance(f, ast.Attribute):
             self.fail(node, f"method call .{f.attr}()")
         if isinstance(f, ast.Lambda):
@@ -1240,6 +1264,10 @@ class _Translator:
                 return self.tmp(INT, "(ks_int)ngpus", bits=4)
             if v.ty in (GPULIST, ILIST, FLIST):
                 return self.tmp(INT, f"(ks_int){v.code}.n", bits=6)
+            if self.is_set(v):
+                if any(it.const is None for it in v.items):
+                    self.fail(node, "len() of a set literal with computed elements")
+                return self.const_val(len({it.const for it in v.items}), node)
             if v.ty == STATIC:
                 return self.const_val(len(v.items), node)
             if v.ty == STR:
@@ -1414,6 +1442,9 @@ class _Translator:
                 self.fail(node, "slice step")
             if base.ty == GPUS:
                 base = self.gpus_to_list()
+            if self.is_dict(base) or self.is_set(base):
+                self.raise_exc()  # TypeError
+                raise _Returned()
             if base.ty == STATIC:
                 lo = self.expr(sl.lower).const if sl.lower is not None else None
                 hi = self.expr(sl.upper).const if sl.upper is not None else None
@@ -1435,6 +1466,16 @@ class _Translator:
             self.emit(f"for (int {q} = {a}; {q} < {b}; ++{q}) {out}.{arr}[{out}.n++] = {base.code}.{arr}[{q}];")
             return Val(base.ty, out)
         idx = self.expr(sl)
+        if self.is_dict(base):
+            if idx.const is None or idx.ty not in (STR, INT):
+                self.fail(node, "dict lookup with a non-constant key")
+            if idx.const not in base.const[1]:
+                self.raise_exc()  # KeyError
+                raise _Returned()
+            return base.items[base.const[1].index(idx.const)]
+        if self.is_set(base):
+            self.raise_exc()  # TypeError: 'set' object is not subscriptable
+            raise _Returned()
         if idx.ty not in (INT, BOOL):
             if base.ty in (GPUS, GPULIST, ILIST, FLIST, STATIC):
                 self.raise_exc()  # TypeError: list indices must be integers
@@ -1545,6 +1586,24 @@ class _Translator:
             if any(isinstance(e, ast.Starred) for e in node.elts):
                 self.fail(node, "starred expression")
             return Val(STATIC, items=[self.expr(e) for e in node.elts])
+        if isinstance(node, ast.Set):
+            # a set literal: only membership (`x in {1, 2, 4}`), len() and truth are order-free; anything that would
+            # iterate it is refused (the iteration order of a set is an implementation detail)
+            if any(isinstance(e, ast.Starred) for e in node.elts):
+                self.fail(node, "starred expression")
+            return Val(STATIC, items=[self.expr(e) for e in node.elts], const="<set>")
+        if isinstance(node, ast.Dict):
+            # a dict literal with constant keys (the usual `weights = {'cpu': 0.6, 'mem': 0.4}`): read by constant key
+            keys = []
+            for k in node.keys:
+                if not (isinstance(k, ast.Constant) and isinstance(k.value, (str, int)) and not isinstance(k.value, bool)):
+                    self.fail(node, "dict literal with non-constant keys")
+                keys.append(k.value)
+            vals = [self.expr(v) for v in node.values]
+            merged = {}
+            for k, v in zip(keys, vals):   # a repeated key keeps its first position and its last value, like CPython
+                merged[k] = v
+            return Val(STATIC, items=list(merged.values()), const=("<dict>", tuple(merged.keys())))
         if isinstance(node, ast.ListComp):
             return self.listcomp(node)
         if isinstance(node, ast.Lambda):
@@ -1727,7 +1786,7 @@ class _Translator:
         A try body therefore either has a bare first handler, which catches everything the policy can raise, or a first
         handler that turns any exception into another exception -- i.e. no handler at all."""
         if s.finalbody:
-            self.fail(s, "try ... finally is not supported")
+            return self.try_finally(s, loop_depth)
         bare = bool(s.handlers) and s.handlers[0].type is None
         if not bare:
             # no effective handler: the body runs as if it were not wrapped (else: follows on normal completion)
@@ -1786,6 +1845,50 @@ class _Translator:
         else:
             return False
         return True
+
+    def try_finally(self, s: ast.Try, loop_depth: int) -> bool:
+        """try [except] [else] finally == try: (try [except] [else]) finally: F.  F runs on the way out of the inner
+        statement, whether it completed or an exception is leaving it; afterwards that exception continues.  Only without
+        return / break / continue anywhere inside (they would have to run F on their way out too)."""
+        for part in (s.body, s.handlers, s.orelse, s.finalbody):
+            for st_ in part:
+                if any(isinstance(n, (ast.Return, ast.Break, ast.Continue)) for n in ast.walk(st_)):
+                    self.fail(s, "return / break / continue inside try ... finally")
+        inner = ast.copy_location(ast.Try(body=s.body, handlers=s.handlers, orelse=s.orelse, finalbody=[]), s)
+        self.ntry += 1
+        k = self.ntry
+        label, done, flag = f"ks_fin{k}", f"ks_fin{k}_ok", f"fin{k}"
+        before = set(self.defined)
+        if not self.try_labels:
+            self.emit("if (st) KS_RETURN(0);")   # a sticky failure from before the statement is not its body's
+        self.emit(f"int {flag} = 0;")
+        self.emit("{")
+        self.ind += 1
+        self.try_labels.append(label)
+        try:
+            if s.handlers or s.orelse:
+                inner_falls = self.stmt(inner, loop_depth)
+            else:
+                inner_falls = self.block(s.body, loop_depth)
+        except _Returned:
+            inner_falls = False
+        finally:
+            self.try_labels.pop()
+        after_inner = set(self.defined)
+        self.ind -= 1
+        self.emit("}")
+        self.emit(f"goto {done};")
+        self.emit(f"{label}: {flag} = 1;")
+        self.emit(f"{done}:;")
+        self.emit(f"if ({flag} && st != 1) KS_RETURN(KS_RET_UNSUPPORTED);")   # leaving the subset is not an exception
+        self.emit(f"if ({flag}) st = 0;")                                      # F computes normally; re-raised below
+        self.defined = set(before)
+        f_falls = self.block(s.finalbody, loop_depth)
+        after_f = set(self.defined)
+        if f_falls:
+            self.emit(f"if ({flag}) {self.exc()}")   # the exception that was leaving continues (to an outer handler or out)
+        self.defined = (after_inner | after_f) if inner_falls else after_f
+        return f_falls and inner_falls
 
     def run(self) -> bool:
         return self.block(self.fn.body[self.skip:])
@@ -1969,7 +2072,7 @@ def compile_policy(source: str) -> CompiledPolicy:
         if isinstance(n, (ast.AsyncFunctionDef, ast.ClassDef)):
             raise PolicyCompileError(f"line {n.lineno}: nested class / async definitions are not supported")
         if isinstance(n, (ast.With, ast.Global, ast.Nonlocal, ast.Yield, ast.YieldFrom, ast.Await, ast.Delete,
-                          ast.NamedExpr, ast.JoinedStr, ast.Dict, ast.Set, ast.DictComp, ast.SetComp, ast.Starred)):
+                          ast.NamedExpr, ast.JoinedStr, ast.DictComp, ast.SetComp, ast.Starred)):
             raise PolicyCompileError(f"line {getattr(n, 'lineno', '?')}: {type(n).__name__} is not supported")
     consts = _module_constants(tree, fn)
     lift, consts, kvalues = _lift_literals(fn, consts)

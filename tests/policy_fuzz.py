@@ -96,6 +96,8 @@ class Gen:
             return f"({a} if {self.cond(d + 1)} else {self.expr(d + 1)})"
         if k < 0.88:
             return f"({a} {r.choice(['and', 'or'])} {self.expr(d + 1)})"
+        if k < 0.895:
+            return f"({a} if pod.num_gpu in {r.choice(['{1, 2, 4}', '(0, 8)', '[1]'])} else {r.choice(INT_LITS)})"
         if k < 0.91:
             return f"math.sqrt(abs({a}))"
         if k < 0.94:
@@ -165,6 +167,8 @@ class Gen:
             s += f"{pad}except{r.choice(['', '', '', ' ZeroDivisionError', ' Exception'])}:\n" + self.block(ind + 1, d + 1)
             if r.random() < 0.3:
                 s += f"{pad}else:\n" + self.block(ind + 1, d + 1)
+            if r.random() < 0.2 and "return" not in s:
+                s += f"{pad}finally:\n{pad}    score = score + {r.choice(['1', '0.5', 'pod.num_gpu'])}\n"
             self.vars = vars_before
             return s
         return f"{pad}return {self.expr(0)}\n"

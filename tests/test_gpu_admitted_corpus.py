@@ -12,7 +12,7 @@ from policy_fuzz import cpython_scores, random_cases
 
 pytestmark = pytest.mark.gpu
 
-DECLINED_CEILING = 0.20   # share of the corpus that may be declined as a whole (round 2)
+DECLINED_CEILING = 0.10   # share of the corpus that may be declined as a whole (round 2: 4 of 50)
 
 HEAD = "def priority_function(pod, node):\n"
 GUARD = ("    if pod.cpu_milli > node.cpu_milli_left or pod.memory_mib > node.memory_mib_left or pod.num_gpu > node.gpu_left:\n"
@@ -72,6 +72,7 @@ CORPUS = {
     "math_sin": HEAD + "    return max(1, int(100 + 50 * math.sin(node.cpu_milli_left / 1000)))\n",
     "list_extend_method": HEAD + "    xs = [1]\n    xs.extend([2, 3])\n    return sum(xs) + 1\n",
     "try_finally": HEAD + "    s = 1\n    try:\n        s = 10 // pod.num_gpu\n    except:\n        s = 2\n    finally:\n        s += 1\n    return s\n",
+    "try_finally_propagates": HEAD + "    s = 1\n    try:\n        s = 10 // (pod.num_gpu - 1)\n    finally:\n        s += node.gpu_left\n    return s\n",
 }
 
 

@@ -93,7 +93,9 @@ def test_template_prefix_is_hoisted_only_when_it_is_exactly_the_template():
     "return round(pod.cpu_milli / 3, -2)",
     "return len(str(pod.cpu_milli))",
     "def helper(x):\n        y = x\n        return y\n    return helper(1)",
-    "d = {}\n    return 1",
+    "d = {}\n    d['a'] = 1\n    return 1",
+    "w = {'a': 1}\n    return sum(w.values())",
+    "return sum(x for x in {1, 2})",
 ])
 def test_unsupported_constructs_are_refused(body):
     from funsearch_kubernetes_simulator_b200.policy_compiler import PolicyCompileError, compile_policy
@@ -141,7 +143,7 @@ def test_compile_pool_translates_compiles_and_links_without_a_gpu(built_lib, tmp
     from funsearch_kubernetes_simulator_b200 import compile_pool
     from funsearch_kubernetes_simulator_b200.policy_compiler import compile_policy
     from funsearch_kubernetes_simulator_b200.variants import policy_population
-    pop = policy_population(24, seed=9) + ["def priority_function(pod, node):\n    return {}\n"]
+    pop = policy_population(24, seed=9) + ["def priority_function(pod, node):\n    return len(f'{pod.num_gpu}')\n"]
     try:
         compile_pool.start(2, 8)
         info = compile_pool.wait_ready()
@@ -149,7 +151,7 @@ def test_compile_pool_translates_compiles_and_links_without_a_gpu(built_lib, tmp
         res, secs = compile_pool.run_jobs("translate", [pop[:12], pop[12:]])
         assert all(r is not None for r in res) and len(secs) == 2
         flat = res[0] + res[1]
-        assert flat[-1][0] == "error" and "Dict" in flat[-1][1]
+        assert flat[-1][0] == "error" and "JoinedStr" in flat[-1][1]
         for src, r in zip(pop[:-1], flat[:-1]):
             cp = compile_policy(src)
             assert (r[1], r[2], tuple(r[3])) == (cp.symbol, cp.flags, cp.consts) and r[0] == cp.cuda_source
