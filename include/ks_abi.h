@@ -86,6 +86,8 @@ typedef long long (*ks_policy_fn)(KS_POLICY_PARAMS);
 #define KS_PF_PREFIX_HOISTED 1  // the source began with the reference template's feasibility prefix
                                 // (funsearch/safe_execution.py:204-216); the kernel evaluates it, the
                                 // function holds only what follows and is called for feasible nodes only
+#define KS_PF_READS_TIME 2      // the function reads pod.creation_time, which a retry changes: its retries are scored on
+                                // every node again (otherwise only on the nodes that changed since the pod last failed)
 struct KsPolicyEntry {
   ks_policy_fn fn;
   long long flags;

@@ -670,3 +670,71 @@ def test_device_exp_log_bit_identical_to_host_libm(env):
     got, want = run(2, xl), host(math.log, xl)
     bad = np.nonzero(got.view(np.uint64) != want.view(np.uint64))[0]
     assert bad.size == 0, f"log: {bad.size} differ, e.g. x={xl[bad[0]]!r} got={got[bad[0]]!r} want={want[bad[0]]!r}"
+
+
+# ---- retries: the kernel rescans only the nodes that changed since the pod last failed, unless the policy sees the time ----
+def _retry_policies():
+    from funsearch_kubernetes_simulator_b200.variants import PREFIX, SUFFIX
+    return {
+        # pure in (pod fields, node rows): the shortcut applies
+        "prefixed_pure": PREFIX + "    score = 1000 - node.cpu_milli_left // 100 + node.gpu_left * 3\n" + SUFFIX,
+        # reads pod.creation_time, which every retry changes: a pod refused for its time alone gets in on a later retry
+        # although no node changed in between, so the shortcut must be off
+        "prefixed_reads_time": PREFIX + "    if pod.creation_time % 5 < 3:\n        return 0\n"
+                                        "    score = 500 + node.memory_mib_left // 1000\n" + SUFFIX,
+        # no template prefix: the function is its own feasibility test and is called for every (changed) node
+        "raw_own_feasibility": "def priority_function(pod, node):\n"
+                               "    if pod.cpu_milli > node.cpu_milli_left or pod.memory_mib > node.memory_mib_left:\n        return 0\n"
+                               "    if pod.num_gpu > node.gpu_left:\n        return 0\n"
+                               "    free = 0\n"
+                               "    for g in node.gpus:\n"
+                               "        if g.gpu_milli_left >= pod.gpu_milli:\n            free += 1\n"
+                               "    if free < pod.num_gpu:\n        return 0\n"
+                               "    return 1 + node.cpu_milli_left // 1000\n",
+        # raw and time-dependent
+        "raw_reads_time": "def priority_function(pod, node):\n"
+                          "    if pod.cpu_milli > node.cpu_milli_left or pod.memory_mib > node.memory_mib_left or pod.num_gpu > node.gpu_left:\n"
+                          "        return 0\n"
+                          "    free = 0\n"
+                          "    for g in node.gpus:\n"
+                          "        if g.gpu_milli_left >= pod.gpu_milli:\n            free += 1\n"
+                          "    if free < pod.num_gpu or (pod.creation_time + pod.duration_time) % 3 == 0:\n        return 0\n"
+                          "    return 7\n",
+    }
+
+
+@pytest.mark.parametrize("width", [1, 4])
+def test_retries_pure_and_time_reading_policies_against_oracle(env, width):
+    """A small cluster under a heavy trace: most events are retries.  Every counter, the placement log and the score
+    against the oracle, for policies with and without the template prefix, pure and time-reading, one warp and teams."""
+    from helpers import oracle_specs, outcome_digest
+    from oracle import pysim
+    from funsearch_kubernetes_simulator_b200 import _native as nat
+    pols = _retry_policies()
+    names = list(pols)
+    for cname, n_nodes, tname, head in (("gpu16", 12, "default", 3000), ("gpu1213", 40, "cpu300", 8000), ("all1523", 48, "gpushare100", 5000)):
+        cluster = env["ClusterSpec"].load(cname).head(n_nodes)
+        tr = env["Trace"].load(tname).head(head)
+        ev = env["BatchEvaluator"](cluster, [tr])
+        ev.warps_per_team = width
+        compiled = ev.compile([pols[n] for n in names])
+        assert all(c is not None for c in compiled)
+        flags = {n: c.flags for n, c in zip(names, compiled)}
+        assert flags["prefixed_pure"] == nat.KS_PF_PREFIX_HOISTED and flags["raw_own_feasibility"] == 0
+        assert flags["prefixed_reads_time"] == nat.KS_PF_PREFIX_HOISTED | nat.KS_PF_READS_TIME
+        assert flags["raw_reads_time"] == nat.KS_PF_READS_TIME
+        outs = ev.run_episodes(compiled, list(range(len(names))), [0] * len(names), want_placements=True)
+        cs, ts = oracle_specs(cluster, tr)
+        retried = 0
+        for n, out in zip(names, outs):
+            ref = pysim.run_episode(cs, ts, pysim.scorer_from_source(pols[n]))
+            tag = (cname, n, width)
+            assert (out.status, out.events, out.attempts, out.placed) == (ref.status, ref.events, ref.attempts, ref.placed), tag
+            assert (out.max_nodes, out.max_waiting, out.last_event_time) == (ref.max_nodes, ref.max_waiting, ref.last_event_time), tag
+            assert outcome_digest(tr, cluster, out) == pysim.placement_digest(ts, cs, ref), tag
+            r = out.results
+            assert (r.num_snapshots, r.num_fragmentation_events) == (ref.num_snapshots, ref.num_fragmentation_events), tag
+            for got, want in ((r.gpu_fragmentation_score, ref.fragmentation), (out.policy_score, ref.score)):
+                assert abs(got - want) <= 1e-9 * max(abs(want), 1e-300), (tag, got, want)
+            retried += ref.attempts - ref.placed
+        assert retried > 1000, "the workload is meant to retry a lot"
