@@ -20,3 +20,9 @@ for n_ep in (148, 1024):
     fails = at - placed
     print(f"n={n_ep}: cyc/event {np.mean(cyc/ev_):.0f} | {names[0]}: {np.mean(a/ev_):.0f}/event ({np.mean(a/np.maximum(placed,1)):.0f}/placement) | "
           f"{names[1]}: {np.mean(b/ev_):.0f}/event ({np.mean(b/np.maximum(fails,1)):.0f}/failed attempt) | events {ev_.mean():.0f} attempts {at.mean():.0f} fails {fails.mean():.0f}", flush=True)
+    # what a placement, a failed attempt (retry) and a deletion cost: least squares over the episodes
+    ok = r["status"] == 0
+    X = np.stack([placed[ok], fails[ok], (ev_ - at)[ok]], axis=1)
+    for nm, y in (("total", cyc[ok]), (names[0], a[ok]), (names[1], b[ok])):
+        coef, *_ = np.linalg.lstsq(X, y, rcond=None)
+        print(f"    {nm:>20s}: {coef[0]:7.0f} cycles/placement  {coef[1]:7.0f} /failed attempt  {coef[2]:7.0f} /deletion", flush=True)
