@@ -30,6 +30,7 @@ KS_MAX_TIME = (1 << 39) - 2
 KS_STATIC_SCRATCH_BYTES = 32 << 20
 KS_PF_PREFIX_HOISTED = 1
 KS_PF_READS_TIME = 2
+KS_PF_READS_DURATION = 4
 KS_MAX_TABLE = 4096
 KS_API_VERSION = 3
 

@@ -2129,6 +2129,8 @@ def compile_policy(source: str) -> CompiledPolicy:
     text = "\n".join(body) + "\n"
     if "p_ctime" in text:
         flags |= 2   # KS_PF_READS_TIME: the one pod field a retry changes (main.py:118-121); the kernel then rescans all nodes
+    if "p_dur" in text:
+        flags |= 4   # KS_PF_READS_DURATION: pods of one request shape may score differently; no per-shape score rows
     # the structure's name is the hash of its code: equal code <=> one device function, whatever source it came from
     symbol = "ks_st_" + hashlib.sha256(f"{flags}|{len(kvalues)}|".encode() + text.encode()).hexdigest()[:20]
     head = (f"// policy structure {symbol}: a priority_function(pod, node) with its {len(kvalues)} float literals in kf[]\n"

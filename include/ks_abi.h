@@ -66,7 +66,8 @@
 #define KS_POD_DUR_LO 4
 #define KS_POD_DUR_HI 5
 #define KS_POD_ORIG_INDEX 6
-#define KS_POD_RESERVED 7
+#define KS_POD_SHAPE 7  // 1 + rank of the pod's (cpu_milli, memory_mib, num_gpu, gpu_milli) among the trace's distinct request
+                        // shapes, most frequent first (ks_trace_pack); 0 = not ranked (the kernel then keeps no scores for it)
 #define KS_POD_INTS 8
 
 // ---- policy function ABI (v3) ----------------------------------------------------------
@@ -81,6 +82,7 @@
   int p_cpu, int p_mem, int p_ngpu, int p_gmilli, long long p_ctime, long long p_dur, unsigned ns, const int *__restrict__ nc, \
       const double *__restrict__ kf
 typedef long long (*ks_policy_fn)(KS_POLICY_PARAMS);
+#define KS_SHAPE_SLOTS 256  // request shapes per episode whose scores per node are kept (teams of warps)
 #define KS_MAX_TABLE 4096  // policy structures one linked module can dispatch to
 // flags of a dispatch-table entry
 #define KS_PF_PREFIX_HOISTED 1  // the source began with the reference template's feasibility prefix
@@ -88,6 +90,8 @@ typedef long long (*ks_policy_fn)(KS_POLICY_PARAMS);
                                 // function holds only what follows and is called for feasible nodes only
 #define KS_PF_READS_TIME 2      // the function reads pod.creation_time, which a retry changes: its retries are scored on
                                 // every node again (otherwise only on the nodes that changed since the pod last failed)
+#define KS_PF_READS_DURATION 4  // the function reads pod.duration_time: pods of one request shape may score differently, so
+                                // the kernel keeps no per-shape scores for it (teams of warps, see KS_SHAPE_SLOTS)
 struct KsPolicyEntry {
   ks_policy_fn fn;
   long long flags;
@@ -140,12 +144,14 @@ struct KsLaunch {
   long long scratch_per_team;
   long long scratch_place_off;  // byte offset of the placement records inside a team's scratch (if not an output)
   long long scratch_wait_off;   // byte offset of the waiting list inside a team's scratch
+  long long scratch_shape_off;  // teams of warps: byte offset of the per-shape stamps and score rows inside a team's scratch
   long long tot_cpu, tot_mem, tot_gpu_count, tot_gpu_milli;
   long long max_events;  // 0 = unlimited
   double snapshot_interval;
   int n_episodes;
   int n_nodes;
   int n_pad;
+  int shape_slots;        // teams of warps: request shapes whose scores per node are kept between attempts (0 = none)
   int class_slots;        // teams of warps: entries of the node-class table in shared memory (a power of two >= 2 * n_pad)
   int heap_smem_entries;  // reserved (0): the heap lives in the team's scratch, L1-resident
   int wait_smem_entries;  // reserved (0)

@@ -682,6 +682,8 @@ def _retry_policies():
         # although no node changed in between, so the shortcut must be off
         "prefixed_reads_time": PREFIX + "    if pod.creation_time % 5 < 3:\n        return 0\n"
                                         "    score = 500 + node.memory_mib_left // 1000\n" + SUFFIX,
+        # reads pod.duration_time: pods of one request shape score differently, so no scores are kept per shape (teams)
+        "prefixed_reads_duration": PREFIX + "    score = 100 + (pod.duration_time % 97) * (node.gpu_left + 1) + node.cpu_milli_left // 500\n" + SUFFIX,
         # no template prefix: the function is its own feasibility test and is called for every (changed) node
         "raw_own_feasibility": "def priority_function(pod, node):\n"
                                "    if pod.cpu_milli > node.cpu_milli_left or pod.memory_mib > node.memory_mib_left:\n        return 0\n"
@@ -703,7 +705,7 @@ def _retry_policies():
     }
 
 
-@pytest.mark.parametrize("width", [1, 4])
+@pytest.mark.parametrize("width", [1, 2, 16])
 def test_retries_pure_and_time_reading_policies_against_oracle(env, width):
     """A small cluster under a heavy trace: most events are retries.  Every counter, the placement log and the score
     against the oracle, for policies with and without the template prefix, pure and time-reading, one warp and teams."""
@@ -722,7 +724,8 @@ def test_retries_pure_and_time_reading_policies_against_oracle(env, width):
         flags = {n: c.flags for n, c in zip(names, compiled)}
         assert flags["prefixed_pure"] == nat.KS_PF_PREFIX_HOISTED and flags["raw_own_feasibility"] == 0
         assert flags["prefixed_reads_time"] == nat.KS_PF_PREFIX_HOISTED | nat.KS_PF_READS_TIME
-        assert flags["raw_reads_time"] == nat.KS_PF_READS_TIME
+        assert flags["raw_reads_time"] == nat.KS_PF_READS_TIME | nat.KS_PF_READS_DURATION
+        assert flags["prefixed_reads_duration"] == nat.KS_PF_PREFIX_HOISTED | nat.KS_PF_READS_DURATION
         outs = ev.run_episodes(compiled, list(range(len(names))), [0] * len(names), want_placements=True)
         cs, ts = oracle_specs(cluster, tr)
         retried = 0

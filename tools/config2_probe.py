@@ -1,5 +1,6 @@
 """BASELINE configs[2] shape: 64 policies x a synthetic Alibaba-shaped trace x 1,024 nodes, by team width
-(python tools/config2_probe.py [pods] [widths...])."""
+(python tools/config2_probe.py [pods] [widths...]; KS_EVENT_BUDGET=<n> caps the events of an episode like bench.py --config 2;
+with a KS_PHASE_CLOCKS build (KS_B200_LIB=<that .so>) the phase sums of the slowest episodes are printed)."""
 import os
 import sys
 
@@ -22,7 +23,7 @@ compiled = ev.compile(pop)
 assert all(c is not None for c in compiled)
 for W in widths:
     ev.warps_per_team = W
-    rb = ev.prepare_resident(compiled, list(range(64)), [0] * 64, single_module=True)
+    rb = ev.prepare_resident(compiled, list(range(64)), [0] * 64, single_module=True, max_events=int(os.environ.get("KS_EVENT_BUDGET", "0")))
     rb.launch()
     torch.cuda.synchronize()
     e0 = torch.cuda.Event(enable_timing=True)
@@ -41,8 +42,10 @@ for W in widths:
         print(f"   phase clocks (KS_PHASE_CLOCKS={os.environ.get('KS_PHASE_CLOCKS')}): a/event {np.mean(pa / ev_):.0f}  b/event {np.mean(pb / ev_):.0f}  "
               f"a/attempt {np.mean(pa / at):.0f}  b/attempt {np.mean(pb / at):.0f}  max_wait mean {r['max_waiting'].mean():.0f} "
               f"frag events/ep {r['num_fragmentation_events'].mean():.0f}")
-    for i in np.argsort(-cyc)[:3]:
-        print(f"   slow ep {i}: {cyc[i] / 1e6:.0f} Mcyc events {r['events'][i]} attempts {r['attempts'][i]} frag {r['num_fragmentation_events'][i]} "
+    okk = np.nonzero(r['status'] == 0)[0]
+    for i in list(np.argsort(-cyc)[:3]) + list(okk[np.argsort(-cyc[okk])][:2]):
+        print(f"   slow ep {i} status {r['status'][i]}: {cyc[i] / 1e6:.0f} Mcyc events {r['events'][i]} attempts {r['attempts'][i]} placed {r['placed'][i]} frag {r['num_fragmentation_events'][i]} "
+              f"max_wait {r['max_waiting'][i]} a/event {pa[i] / ev_[i]:.0f} b/event {pb[i] / ev_[i]:.0f} "
               f"cyc/event {cyc[i] / ev_[i]:.0f} hoisted {compiled[i].flags} consts {len(compiled[i].consts)} src lines {pop[i].count(chr(10))}")
     print(f"   all episodes: sum(cyc)/sum(events) = {cyc.sum() / ev_.sum():.0f}")
     print(f"W={W:2d} teams/blk {rb.plan.teams_per_block} blocks {rb.plan.blocks} smem/blk {rb.plan.smem_per_block}: {ms:9.1f} ms  "
