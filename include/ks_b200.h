@@ -46,7 +46,10 @@ int ks_init(int device);
  * (simulator/event_simulator.py:23-34) over Pod objects (simulator/entities.py:30-43) produced by
  * TraceParser.parse_pods (benchmarks/parser.py:68-101).
  *   id_rank[i] = rank of pod i's pod_id in string order (Event.__lt__, event_simulator.py:16-17)
- *   podrec  [n_pods * KS_POD_INTS] ints, heap0 [n_pods], place0 [n_pods]: caller-allocated host arrays */
+ *   podrec  [n_pods * KS_POD_INTS] ints, heap0 [n_pods], place0 [n_pods]: caller-allocated host arrays
+ * A pod record also carries the rank of the pod's request shape (cpu_milli, memory_mib, num_gpu, gpu_milli) among the
+ * trace's distinct shapes, commonest first (KS_POD_SHAPE): on clusters replayed by teams of warps the kernel keeps each
+ * node's score per shape and rescores only the nodes that changed since the shape's last pod. */
 int ks_trace_pack(long long n_pods, const int* cpu_milli, const int* memory_mib, const int* num_gpu,
                   const int* gpu_milli, const long long* creation_time, const long long* duration_time,
                   const int* id_rank, int* podrec, unsigned long long* heap0, unsigned long long* place0);
@@ -66,7 +69,9 @@ int ks_cluster_pack(int n_nodes, const int* cpu_total, const int* mem_total, con
  *     extern "C" __device__ long long <symbol>(KS_POLICY_PARAMS)          (include/ks_abi.h)
  * (what the Python-AST translator emits: the policy with its float literals lifted into the argument `kf`, so that
  * all policies that differ only in those constants share one function), with NVRTC for sm_100a into a relocatable
- * cubin.  `flags` are the KS_PF_* bits the dispatch table will carry for this function.  Results
+ * cubin.  `flags` are the KS_PF_* bits the dispatch table will carry for this function (KS_PF_READS_TIME and
+ * KS_PF_READS_DURATION are added by the library when the source mentions p_ctime / p_dur: the kernel's retry shortcut and
+ * its per-shape score rows are only valid for functions that do not see those fields).  Results
  * are cached by source hash (in memory, and on disk when ks_set_cache_dir was called).
  * Replaces: FunSearchScheduler._compile_policy, exec of the policy source
  * (funsearch/funsearch_integration.py:77-89).  *policy receives a handle valid until ks_shutdown. */
