@@ -59,6 +59,9 @@ def workload_config(args):
          "population_per_rank": "same" if args.population == "same" else "seed + rank"}
     if args.config == 3:
         c["candidates"] = args.candidates
+    if args.config == 2:
+        c["policies_per_gpu"] = args.policies_per_gpu
+        c["workload"] = c["workload"].replace("64 policies", f"{args.policies_per_gpu} policies per GPU")
     return c
 
 
@@ -173,8 +176,9 @@ def build_workload(args, rank, world):
         cluster = ClusterSpec.load("all1523").head(1024)
         traces = [synthetic_trace(args.pods or 1000000, seed=3, load_factor=200.0)]
         shipped = json.load(open(os.path.join(ROOT, "tests", "golden", "policies.json")))
-        pop = policy_population(64 - len(C_ORACLE_POLICIES), seed=seed) + [shipped[k] for k in C_ORACLE_POLICIES]
-        return cluster, traces, pop, list(range(64)), [0] * 64, None
+        npol = args.policies_per_gpu
+        pop = policy_population(npol - len(C_ORACLE_POLICIES), seed=seed) + [shipped[k] for k in C_ORACLE_POLICIES]
+        return cluster, traces, pop, list(range(npol)), [0] * npol, None
     if args.config == 3:
         cluster = ClusterSpec.load("gpu16")
         names = ["default", "cpu037", "cpu050", "cpu072", "cpu100", "cpu200", "cpu235", "cpu250", "cpu300", "gpushare20",
@@ -711,6 +715,8 @@ def main():
     ap.add_argument("--episodes", type=int, default=0, help="configs 1/4: episodes per GPU (default 1024)")
     ap.add_argument("--pods", type=int, default=0, help="config 2: pods of the synthetic trace (default 1,000,000)")
     ap.add_argument("--candidates", type=int, default=1024, help="config 3: policies in the population")
+    ap.add_argument("--policies-per-gpu", type=int, default=64,
+                    help="config 2: policies (= episodes) per GPU; 64 is configs[2], 128 is the north-star shape (1,024 policies on 8 GPUs)")
     ap.add_argument("--fresh-steps", type=int, default=2, help="timed fresh generations for e2e_fresh (0 = skip)")
     ap.add_argument("--teams", type=int, default=0, help="warps (episodes) per CTA; 0 = planner's choice")
     ap.add_argument("--no-cpu-baseline", action="store_true")
