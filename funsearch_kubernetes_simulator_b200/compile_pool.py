@@ -178,6 +178,10 @@ def start(processes: int, batch: int) -> str:
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
     env = dict(os.environ)
     env["PYTHONPATH"] = root + os.pathsep + env.get("PYTHONPATH", "")
+    # On a machine with the NVIDIA driver NVRTC keeps its results in the driver's compute cache (~/.nv/ComputeCache).  A
+    # generation's programs never repeat (structures that do are found in ks_set_cache_dir's cache before NVRTC is asked),
+    # so that cache would only be written (about 20 MB per generation of 1,024 sources), never hit.
+    env.setdefault("CUDA_CACHE_DISABLE", "1")
     _WORKERS[:] = [w for w in _WORKERS if w.alive()]
     while len(_WORKERS) < processes:
         _WORKERS.append(_Worker(subprocess.Popen(
