@@ -204,3 +204,48 @@ def test_plan_team_shapes(built_lib):
     q.warps_per_team = 1
     nat.check(nat.lib().ks_plan(C.byref(q)))
     assert q.ctas_per_sm == 2 and q.blocks == 296 and q.teams_per_block == 8
+
+
+def test_trace_pack_ranks_request_shapes(built_lib):
+    """Slot 7 of a pod record = 1 + rank of the pod's (cpu, mem, gpus, gpu milli) among the trace's distinct request shapes,
+    commonest first, ties by first appearance (the team kernels key their per-node score rows by it)."""
+    from collections import Counter
+    from funsearch_kubernetes_simulator_b200 import Trace, synthetic_trace
+    for tr in (Trace.load("default"), Trace.load("gpushare60").head(3000), synthetic_trace(5000, seed=3, load_factor=200.0)):
+        rank, podrec, _heap0, _place0 = tr.packed()
+        shapes = list(zip(tr.cpu_milli.tolist(), tr.memory_mib.tolist(), tr.num_gpu.tolist(), tr.gpu_milli.tolist()))
+        count = Counter(shapes)
+        first = {}
+        for i, s in enumerate(shapes):
+            first.setdefault(s, i)
+        order = sorted(count, key=lambda s: (-count[s], first[s]))
+        want = {s: k + 1 for k, s in enumerate(order)}
+        got = [int(podrec[int(rank[i]) * 8 + 7]) for i in range(tr.n_pods)]
+        assert got == [want[s] for s in shapes], tr.name
+        assert max(got) == len(count)
+
+
+def test_team_plans_carry_score_rows_and_flags_mark_time_readers(built_lib):
+    """Scratch of a team of warps holds 256 score rows (8 B x n_pad each) + their stamps on top of heap, placement records,
+    waiting list and failure stamps; one-warp plans hold none.  The translator flags functions that read the pod's time fields."""
+    from funsearch_kubernetes_simulator_b200 import _native as nat
+    from funsearch_kubernetes_simulator_b200.policy_compiler import compile_policy
+    from funsearch_kubernetes_simulator_b200.variants import PREFIX, SUFFIX
+    solo, team = nat.KsPlan(), nat.KsPlan()
+    solo.n_episodes, solo.n_nodes, solo.max_pods = 1024, 16, 8152
+    team.n_episodes, team.n_nodes, team.max_pods = 64, 1024, 8152
+    nat.check(nat.lib().ks_plan(C.byref(solo)))
+    nat.check(nat.lib().ks_plan(C.byref(team)))
+    base = 8152 * 8 * 2 + 8152 * 12          # heap + placement records + (waiting list, failure stamps)
+    assert solo.warps_per_team == 1 and base <= solo.scratch_per_team < base + 1024
+    rows = 256 * (4 + 8 * 1024)
+    assert team.warps_per_team == 16 and base + rows <= team.scratch_per_team < base + rows + 1024
+    flags = lambda body: compile_policy(PREFIX + body + SUFFIX).flags  # noqa: E731
+    assert flags("    score = node.cpu_milli_left // 10\n") == nat.KS_PF_PREFIX_HOISTED
+    assert flags("    score = pod.creation_time % 7 + 1\n") == nat.KS_PF_PREFIX_HOISTED | nat.KS_PF_READS_TIME
+    assert flags("    score = pod.duration_time % 7 + 1\n") == nat.KS_PF_PREFIX_HOISTED | nat.KS_PF_READS_DURATION
+    # a hand-written function that mentions the arguments gets the flags from the library itself
+    src = 'extern "C" __device__ long long ks_hand_t(KS_POLICY_PARAMS) { return 1 + (p_ctime & 1) + (p_dur & 1); }\n'
+    h = C.c_longlong(-1)
+    nat.check(nat.lib().ks_policy_compile(src.encode(), b"ks_hand_t", 0, C.byref(h)))
+    assert h.value >= 0
