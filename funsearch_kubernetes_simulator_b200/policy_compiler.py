@@ -170,23 +170,36 @@ class _Translator:
         if len(args) != 2 or fn.args.vararg or fn.args.kwarg or fn.args.kwonlyargs or fn.args.defaults:
             raise PolicyCompileError("priority_function must take exactly (pod, node)")
         self.pod_name, self.node_name = args
-        self.assign_count: Dict[str, int] = {}
+        # what the function's text alone decides is scanned once per function, not once per pass of the type fixed point
+        scan = getattr(fn, "_ks_scan", None)
+        if scan is None:
+            scan = fn._ks_scan = self._scan(fn)
+        self.appended, counts = scan
+        self.assign_count: Dict[str, int] = dict(counts)
+
+    @staticmethod
+    def _scan(fn: ast.FunctionDef):
+        assign_count: Dict[str, int] = {}
         # names that are built up with .append(): `xs = []` then `xs.append(v)` in loops / branches
-        self.appended = {n.func.value.id for n in ast.walk(fn) if isinstance(n, ast.Call) and isinstance(n.func, ast.Attribute)
-                         and n.func.attr in ("append", "extend") and isinstance(n.func.value, ast.Name)}
-        for n in ast.walk(fn):
-            if isinstance(n, (ast.Assign, ast.AugAssign, ast.AnnAssign)):
+        appended = set()
+        for n in (getattr(fn, "_ks_nodes", None) or ast.walk(fn)):
+            if isinstance(n, ast.Call):
+                if (isinstance(n.func, ast.Attribute) and n.func.attr in ("append", "extend")
+                        and isinstance(n.func.value, ast.Name)):
+                    appended.add(n.func.value.id)
+            elif isinstance(n, (ast.Assign, ast.AugAssign, ast.AnnAssign)):
                 tg = n.targets if isinstance(n, ast.Assign) else [n.target]
                 for t in tg:
-                    for nm in ast.walk(t):
+                    for nm in ([t] if isinstance(t, ast.Name) else ast.walk(t)):
                         if isinstance(nm, ast.Name):
-                            self.assign_count[nm.id] = self.assign_count.get(nm.id, 0) + 1
+                            assign_count[nm.id] = assign_count.get(nm.id, 0) + 1
             elif isinstance(n, (ast.For,)):
-                for nm in ast.walk(n.target):
+                for nm in ([n.target] if isinstance(n.target, ast.Name) else ast.walk(n.target)):
                     if isinstance(nm, ast.Name):
-                        self.assign_count[nm.id] = self.assign_count.get(nm.id, 0) + 2
+                        assign_count[nm.id] = assign_count.get(nm.id, 0) + 2
             elif isinstance(n, ast.FunctionDef) and n is not fn:
-                self.assign_count[n.name] = self.assign_count.get(n.name, 0) + 1
+                assign_count[n.name] = assign_count.get(n.name, 0) + 1
+        return appended, assign_count
 
     # ------------------------------------------------------------------ emission helpers
     def emit(self, s: str):
@@ -1996,9 +2009,17 @@ def _hoistable_prefix(fn: ast.FunctionDef) -> int:
     mapping = {pod: "pod", node: "node", cnt: "available_gpus", gpu: "gpu"}
     if len(set(mapping)) != 4 or {cnt, gpu} & {"pod", "node"}:
         return 0
-    ren = _Rename(mapping)
-    import copy
-    if [ast.dump(ren.visit(copy.deepcopy(x))) for x in (a, b)] != _PREFIX_DUMP:
+    # compare under the renaming without copying the statements: the names are mapped in place for the dump and put back
+    names = [n for x in (a, b) for n in ast.walk(x) if isinstance(n, ast.Name)]
+    saved = [n.id for n in names]
+    try:
+        for n in names:
+            n.id = mapping.get(n.id, n.id)
+        same = [ast.dump(x) for x in (a, b)] == _PREFIX_DUMP
+    finally:
+        for n, old in zip(names, saved):
+            n.id = old
+    if not same:
         return 0
     if _reads_outside_own_binding(body[k + 2:], {cnt, gpu}):
         return 0
@@ -2036,12 +2057,21 @@ def _lift_literals(fn: ast.FunctionDef, consts: Dict[str, object]):
     values: List[float] = []
     lift: Dict[int, int] = {}
 
-    class V(ast.NodeVisitor):
-        def visit_Constant(self, node):
+    def visit(node):   # document order, like ast.NodeVisitor
+        if type(node) is ast.Constant:
             if _is_lifted_value(node.value):
                 lift[id(node)] = len(values)
                 values.append(node.value)
-    V().visit(fn)
+            return
+        for f in node._fields:
+            v = getattr(node, f, None)
+            if type(v) is list:
+                for x in v:
+                    if isinstance(x, ast.AST):
+                        visit(x)
+            elif isinstance(v, ast.AST):
+                visit(v)
+    visit(fn)
 
     def mark(c):
         if _is_lifted_value(c):
@@ -2068,7 +2098,8 @@ def compile_policy(source: str) -> CompiledPolicy:
     if not fns:
         raise PolicyCompileError("no priority_function defined")
     fn = fns[-1]
-    for n in ast.walk(fn):
+    fn._ks_nodes = list(ast.walk(fn))   # walked once: the checks below and _Translator._scan go over the list
+    for n in fn._ks_nodes:
         if isinstance(n, (ast.AsyncFunctionDef, ast.ClassDef)):
             raise PolicyCompileError(f"line {n.lineno}: nested class / async definitions are not supported")
         if isinstance(n, (ast.With, ast.Global, ast.Nonlocal, ast.Yield, ast.YieldFrom, ast.Await, ast.Delete,
