@@ -277,6 +277,7 @@ class BatchEvaluator:
                 res, secs = compile_pool.run_jobs("nvrtc_link", [(gs, img) for gs, img in zip(per_worker, images)])
                 stats["pool_workers"] = compile_pool.n_workers()
                 stats["worker_nvrtc_link_s_max"] = max(secs) if secs else 0.0
+                stats["worker_nvrtc_link_s_mean"] = sum(secs) / len(secs) if secs else 0.0
                 stats["nvrtc_link_s"] = time.perf_counter() - t0
                 t0 = time.perf_counter()
                 self._register_groups(groups, 1)   # cubins are in the shared cache: these are hits
